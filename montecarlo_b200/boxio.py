@@ -1,0 +1,232 @@
+"""Input files of the Fortran driver, read and written on the host.
+
+The driver keeps its own formats (reference MonteCarlo/MonteCarlo.F90:1053-1166 `read_norm`,
+:587-611 result writer, :1009-1019 `dump`); this module reads and writes the same text so that
+C++/Python harnesses can stand in for the driver where no Fortran compiler exists, and so the
+inputs of configs 3-5 (replicated boxes) can be generated.  Nothing here computes an energy.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field, replace
+from pathlib import Path
+
+import numpy as np
+
+ENERGY_ABSENT = 123456.789  # sentinel, reference MonteCarlo.F90:1090
+
+
+def _f(tok: str) -> float:
+    return float(tok.replace("D", "E").replace("d", "e"))
+
+
+@dataclass
+class Box:
+    """One box file (reference MonteCarlo.F90:1084-1126; layout in SURVEY.md appendix A)."""
+    boxl: float                      # HALF the box side, Angstrom (reference BOXL)
+    com: np.ndarray                  # [N][3] centres of mass
+    hoek: np.ndarray                 # [N][3] Euler angles (radians)
+    energy: float = ENERGY_ABSENT    # line 3, energy of the previous run
+    box_id: str = "BOX"
+    sol_sym: list[str] = field(default_factory=list)
+    solute: np.ndarray = field(default_factory=lambda: np.zeros((0, 3)))
+    sol_name: str = ""
+    e_sol: float = 0.0               # Hartree
+    dihedrals: list[tuple[int, int, float]] = field(default_factory=list)
+
+    @property
+    def n(self) -> int:
+        return int(self.com.shape[0])
+
+    @property
+    def nsol(self) -> int:
+        return int(self.solute.shape[0])
+
+
+def read_box(path: str | Path) -> Box:
+    """Reads the current box format (reference MonteCarlo.F90:1078-1128)."""
+    lines = Path(path).read_text().splitlines()
+    boxl = _f(lines[0].split()[0])
+    n = int(lines[1].split()[0])
+    p = 2
+    energy = ENERGY_ABSENT
+    try:  # READ "(E20.10)": a line that does not parse as a number is the ID line (:1086-1092)
+        energy = _f(lines[p].split()[0])
+        p += 1
+    except (ValueError, IndexError):
+        pass
+    box_id = lines[p].strip()
+    p += 1
+    vals = np.array([[_f(t) for t in lines[p + i].split()[:6]] for i in range(n)], dtype=np.float64)
+    p += n
+    box = Box(boxl=boxl, com=vals[:, 0:3].copy(), hoek=vals[:, 3:6].copy(), energy=energy, box_id=box_id)
+    if p < len(lines) and lines[p].strip().upper().startswith("SOLUTE"):
+        p += 1
+        nsol = int(lines[p].split()[0]); p += 1
+        box.sol_name = lines[p].rstrip("\n"); p += 1
+        syms, xyz = [], []
+        for i in range(nsol):
+            t = lines[p + i].split()
+            syms.append(t[0]); xyz.append([_f(t[1]), _f(t[2]), _f(t[3])])
+        p += nsol
+        box.sol_sym, box.solute = syms, np.array(xyz, dtype=np.float64).reshape(nsol, 3)
+        box.e_sol = _f(lines[p].split()[0]); p += 1
+        ndih = int(lines[p].split()[0]); p += 1
+        for i in range(ndih):  # (I3,1X,I3,1X,F10.6)
+            t = lines[p + i].split()
+            box.dihedrals.append((int(t[0]), int(t[1]), _f(t[2])))
+    return box
+
+
+def write_box(box: Box, path: str | Path) -> None:
+    """Writes a box the reference's `read_norm` accepts (17 significant digits round-trip fp64)."""
+    out = [f"  {box.boxl:.17g}", f"  {box.n:d}"]
+    e = box.energy if box.energy != ENERGY_ABSENT else 0.0
+    out.append(f"{e:20.10E}")
+    out.append(f" {box.box_id}")
+    for c, h in zip(box.com, box.hoek):
+        out.append(" ".join(f"{v:.17g}" for v in (*c, *h)))
+    out.append(" SOLUTE")
+    out.append(f"  {box.nsol:d}")
+    out.append(box.sol_name)
+    for s, x in zip(box.sol_sym, box.solute):
+        out.append(f" {s:<3s} " + " ".join(f"{v:.17g}" for v in x))
+    out.append(f"  {box.e_sol:.17g}")
+    out.append(f"  {len(box.dihedrals):d}")
+    for a, b, r in box.dihedrals:
+        out.append(f"{a:3d} {b:3d} {r:10.6f}")
+    Path(path).write_text("\n".join(out) + "\n")
+
+
+def box_text(box: Box) -> str:
+    import io, tempfile, os
+    fd, name = tempfile.mkstemp(suffix=".box")
+    os.close(fd)
+    try:
+        write_box(box, name)
+        return Path(name).read_text()
+    finally:
+        os.unlink(name)
+
+
+def read_dmso(path: str | Path):
+    """Solvent geometry file (reference MonteCarlo.F90:1066-1074): n, comment, n x `sym x y z`, E (Hartree)."""
+    lines = Path(path).read_text().splitlines()
+    n = int(lines[0].split()[0])
+    syms, rel = [], []
+    for i in range(n):
+        t = lines[2 + i].split()
+        syms.append(t[0]); rel.append([_f(t[1]), _f(t[2]), _f(t[3])])
+    e = _f(lines[2 + n].split()[0])
+    return syms, np.array(rel, dtype=np.float64), e
+
+
+def read_param(path: str | Path):
+    """param.txt (reference MonteCarlo.F90:1138-1146): n, comment, n x `sym q eps sigma [mass]`."""
+    lines = Path(path).read_text().splitlines()
+    n = int(lines[0].split()[0])
+    syms, tab = [], []
+    for i in range(n):
+        t = lines[2 + i].split()
+        syms.append(t[0]); tab.append([_f(t[1]), _f(t[2]), _f(t[3])])
+    return syms, np.array(tab, dtype=np.float64)
+
+
+def read_par_solute(path: str | Path):
+    """par_solute.txt (reference MonteCarlo.F90:1155-1162): n, comment, n x `sym eps sigma`."""
+    lines = Path(path).read_text().splitlines()
+    n = int(lines[0].split()[0])
+    syms, tab = [], []
+    for i in range(n):
+        t = lines[2 + i].split()
+        syms.append(t[0]); tab.append([_f(t[1]), _f(t[2])])
+    return syms, np.array(tab, dtype=np.float64)
+
+
+def _find_sym(sym: str, table_syms: list[str]) -> int:
+    """findSym (reference MC_lib/lib.f90:87-107): first match, a miss falls back to row 1."""
+    for i, s in enumerate(table_syms):
+        if s == sym:
+            return i
+    return 0
+
+
+def associate_dmso(syms, par_syms, par_tab):
+    """ASSOSIATE_DMSO (reference LennardJones.f90:192-219): (q, eps, sigma) per solvent atom.
+    Hydrogen rows are never filled by the reference (and never read: LennardJones.f90:66,68);
+    they are zero here."""
+    tab = np.zeros((len(syms), 3), dtype=np.float64)
+    is_h = np.array([1 if s == "H" else 0 for s in syms], dtype=np.int32)
+    for i, s in enumerate(syms):
+        if s != "H":
+            tab[i] = par_tab[_find_sym(s, par_syms)]
+    return tab, is_h
+
+
+def associate_solute(syms, par_syms, par_tab, charges=None):
+    """ASSOSIATE_SOLUTE (reference LennardJones.f90:224-248): q = 0 unless the driver supplies
+    CHELPG charges afterwards (MonteCarlo.F90:353)."""
+    tab = np.zeros((len(syms), 3), dtype=np.float64)
+    for i, s in enumerate(syms):
+        a = _find_sym(s, par_syms)
+        tab[i, 1:3] = par_tab[a]
+    if charges is not None:
+        tab[:, 0] = np.asarray(charges, dtype=np.float64)
+    return tab
+
+
+def replicate(box: Box, k: int) -> Box:
+    """Periodic k x k x k replication (new; the reference's BoxScale only rescales at constant N,
+    BoxScale/BoxScale.f08:31-40).  Offsets (m - (k-1)/2) * 2*BOXL per axis, BOXL' = k*BOXL, angles copied;
+    one solute, shifted by (+BOXL)^3 for even k so it stays inside a cavity."""
+    if k == 1:
+        return replace(box, com=box.com.copy(), hoek=box.hoek.copy(), solute=box.solute.copy())
+    side = 2.0 * box.boxl
+    coms, hoeks = [], []
+    for mz in range(k):
+        for my in range(k):
+            for mx in range(k):
+                off = (np.array([mx, my, mz], dtype=np.float64) - (k - 1) / 2.0) * side
+                coms.append(box.com + off)
+                hoeks.append(box.hoek.copy())
+    solute = box.solute + (box.boxl if k % 2 == 0 else 0.0)
+    return replace(box, boxl=k * box.boxl, com=np.concatenate(coms), hoek=np.concatenate(hoeks),
+                   solute=solute, box_id=f"{box.box_id} x{k}^3")
+
+
+def scale(box: Box, factor: float) -> Box:
+    """BoxScale (reference BoxScale/BoxScale.f08:31-40): BOXL and every CoM times `factor`, N unchanged."""
+    return replace(box, boxl=box.boxl * factor, com=box.com * factor, hoek=box.hoek.copy())
+
+
+@dataclass
+class System:
+    """Everything the energy path needs besides the per-chain state: the reference's DMSO, DMSO_SYM,
+    TABLE_DMSO, SOLUTE, TABLE_SOL, BOXL (MonteCarlo.F90:306-310), reduced to the sites that interact."""
+    boxl: float
+    dmso_sym: list[str]
+    dmso_rel: np.ndarray     # [ndmso][3]
+    dmso_tab: np.ndarray     # [ndmso][3]
+    dmso_is_h: np.ndarray    # [ndmso] int32
+    sol_sym: list[str]
+    solute: np.ndarray       # [nsol][3]
+    sol_tab: np.ndarray      # [nsol][3]
+    conv: float = 0.0        # reference value (LennardJones.f90:57)
+    cutoff: float = 7.0      # MonteCarlo.F90:812
+
+    @property
+    def site_rel(self) -> np.ndarray:
+        return np.ascontiguousarray(self.dmso_rel[self.dmso_is_h == 0])
+
+    @property
+    def site_tab(self) -> np.ndarray:
+        return np.ascontiguousarray(self.dmso_tab[self.dmso_is_h == 0])
+
+
+def load_system(box: Box, dmso_path, param_path, parsol_path, charges=None, conv: float = 0.0) -> System:
+    dsym, drel, _ = read_dmso(dmso_path)
+    psym, ptab = read_param(param_path)
+    ssym, stab = read_par_solute(parsol_path)
+    dtab, is_h = associate_dmso(dsym, psym, ptab)
+    soltab = associate_solute(box.sol_sym, ssym, stab, charges)
+    return System(boxl=box.boxl, dmso_sym=dsym, dmso_rel=drel, dmso_tab=dtab, dmso_is_h=is_h,
+                  sol_sym=list(box.sol_sym), solute=box.solute.copy(), sol_tab=soltab, conv=conv)

@@ -1,0 +1,168 @@
+"""CPU: the C restatement (oracle/) against fixtures produced by the reference's own binary.
+
+This is what makes the oracle "pinned": every quantity below was written by the unmodified
+MonteCarlo/MonteCarloOpenMP (oracle/make_golden.py), not restated.
+"""
+import json
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from golden_util import (GOLD, C_TOT, C_OLD, C_KANS, C_RV, C_RSOLV, C_RATIO, C_DPOS, C_DHOEK, C_PSUC, load_trace,
+                         recover_uniforms)
+from montecarlo_b200 import boxio
+
+PRINT11 = 6e-11  # `ES20.10` prints 11 significant digits: half a unit in the last place, relative
+
+
+def test_constants():
+    L = ol.lib()
+    assert L.mco_const_e() == 2.7182817459106445           # float literal, reference MC_lib/lib.f90:17
+    assert L.mco_const_hartree2kjmol() == 2625.499267578125  # float32 product, lib.f90:19
+    assert L.mco_const_conv_reference() == 0.0             # LennardJones.f90:57
+    # PostProcess/log030.txt:45-46 print these products of the reference's own constants
+    assert abs(-0.16947515 * L.mco_const_hartree2kjmol() - (-444.956882197693)) < 1e-9
+    assert abs(float(np.float32(-.0499674791107)) * L.mco_const_hartree2kjmol() - (-131.189579414181)) < 1e-9
+    assert abs(0.053 * L.mco_const_pi() - 0.166504410640259) < 1e-15
+
+
+def test_startup_shipped_box(shipped):
+    box, system = shipped
+    g = np.load(GOLD / "ref_startup_k1.npz")
+    ch = ol.OracleChain(system, box.com, box.hoek)
+    e = ch.total_energy()
+    assert abs(e - float(g["initial_energy"])) <= PRINT11 * abs(e)
+    assert abs(e - 2.7968745663e3) <= PRINT11 * abs(e)
+    ss, en = ch.matrix()
+    ref = g["matrix"]
+    assert np.array_equal(ss != 0, ref != 0) and int((ref != 0).sum()) == 340
+    nz = ref != 0
+    assert np.max(np.abs(ss[nz] - ref[nz]) / np.abs(ref[nz])) < 1e-13  # 15 printed digits
+    assert np.array_equal(ss, ss.T)
+    assert abs(ss[0, 2] - (-1.93595228537649)) < 1e-13 and abs(ss[5, 26] - 1235.49700686554) < 1e-10
+    # matrix-free variants hold the same numbers
+    e_mf, es, npair = ch.total_energy_matrixfree()
+    assert e_mf == e and npair == 170 and abs(es - 463.892021002) < 1e-7
+    # the fp128 arbiter agrees far inside the tolerance the GPU is held to
+    q = ol.OracleChain(system, box.com, box.hoek, quad=True).total_energy()
+    assert abs(q - e) < 1e-12 * abs(e)
+
+
+def test_charges_do_not_matter(shipped):
+    """CONV == 0 in the reference: the start-up energy with CHELPG charges is the same number."""
+    box, system = shipped
+    g = json.loads((GOLD / "ref_charges.json").read_text())
+    assert g["matrix_equal_to_uncharged"]
+    tab = system.sol_tab.copy()
+    tab[:, 0] = g["charges"]
+    e = ol.OracleChain(system, box.com, box.hoek, sol_tab=tab).total_energy()
+    assert abs(e - g["initial_energy"]) <= PRINT11 * abs(e)
+    assert e == ol.OracleChain(system, box.com, box.hoek).total_energy()
+
+
+def test_startup_replica_k2(shipped):
+    box, system = shipped
+    g = np.load(GOLD / "ref_startup_k2.npz")
+    b2 = boxio.replicate(box, 2)
+    s2 = boxio.System(**{**system.__dict__, "boxl": b2.boxl, "solute": b2.solute})
+    ch = ol.OracleChain(s2, b2.com, b2.hoek)
+    e = ch.total_energy()
+    assert abs(e - float(g["initial_energy"])) <= PRINT11 * abs(e)
+    ss, _ = ch.matrix()
+    ref = g["matrix"]
+    assert np.array_equal(ss != 0, ref != 0) and int((ref != 0).sum()) == 2720
+    nz = ref != 0
+    assert np.max(np.abs(ss[nz] - ref[nz]) / np.abs(ref[nz])) < 1e-12
+    e_c, _, npair = ch.total_energy_matrixfree(cells=True)
+    assert e_c == ch.total_energy_matrixfree()[0] == e and npair == 1360
+
+
+def test_startup_replica_k5(shipped):
+    box, system = shipped
+    g = json.loads((GOLD / "ref_startup_k5.json").read_text())
+    b5 = boxio.replicate(box, 5)
+    s5 = boxio.System(**{**system.__dict__, "boxl": b5.boxl, "solute": b5.solute})
+    ch = ol.OracleChain(s5, b5.com, b5.hoek, keep_matrix=False)
+    e, es, npair = ch.total_energy_matrixfree(cells=True)
+    assert b5.n == g["n"] == 3750 and 2 * npair == g["nonzero"]
+    assert abs(e - g["initial_energy"]) <= PRINT11 * abs(e)
+    assert abs((e - es) - g["sum_upper"]) < 1e-9 * abs(e)
+    e_b, _, np_b = ch.total_energy_matrixfree(cells=False)
+    assert e_b == e and np_b == npair
+
+
+@pytest.mark.parametrize("name", ["ref_trace_10k.npz", "ref_trace_adapt.npz"])
+def test_replay_reference_trace(shipped, name):
+    """Drive the oracle's MCINIT + calculateLJ + calcEnergy + METROPOLIS with uniforms recovered from the
+    reference's own DUMP/OUT files and compare every printed column of every step."""
+    box, system = shipped
+    t = load_trace(name)
+    rows, moved, acc = t["out_rows"], t["moved"], t["accepted"]
+    temp, dposmax, dposmin, dhoekmax, dhoekmin, padj, nadj = t["params"]
+    ch = ol.OracleChain(system, box.com, box.hoek)
+    ch.set_mc_params(temp, dposmax, dposmin, dhoekmax * np.pi, dhoekmin * np.pi, padj, int(nadj), 0, 1)
+    e0 = ch.total_energy()
+    assert abs(e0 - float(t["initial_energy"])) <= PRINT11 * abs(e0)
+    cur = np.concatenate([box.com, box.hoek], axis=1)
+    nsuc = 0
+    unresolved = 0
+    for k in range(rows.shape[0]):
+        st = ch.stats()
+        i1 = int(rows[k, C_RSOLV])
+        u = recover_uniforms(cur[i1 - 1], moved[k], st["dposmax"], st["dhoekmax"], box.boxl, i1, box.n, acc[k], True)
+        used, tr = ch.step(u)
+        assert int(tr[4]) == i1 - 1
+        com, hoek = ch.get_state()
+        # trial energy and the energy it is compared with, 11 printed digits
+        assert abs(tr[0] - rows[k, C_TOT]) <= 2 * PRINT11 * max(abs(tr[0]), abs(rows[k, C_OLD])), (k, tr[0], rows[k, C_TOT])
+        assert abs(tr[1] - rows[k, C_OLD]) <= 2 * PRINT11 * abs(tr[1]), k
+        # kans / rv columns (F6.4) and the draw-skipping rules of METROPOLIS (MonteCarlo.F90:730-741)
+        assert abs(tr[2] - rows[k, C_KANS]) <= 5.1e-5, (k, tr[2], rows[k, C_KANS])
+        if used == 7:
+            assert rows[k, C_RV] in (0.0, 1.0) and tr[3] == rows[k, C_RV]
+        else:
+            # decision from the PRINTED rv against the oracle's kans, where 4 decimals can resolve it
+            if abs(rows[k, C_RV] - tr[2]) > 1.01e-4:
+                assert (rows[k, C_RV] <= tr[2]) == bool(acc[k]), (k, rows[k, C_RV], tr[2])
+            else:
+                unresolved += 1
+        assert bool(tr[5]) == bool(acc[k])
+        nsuc += int(acc[k])
+        assert abs(tr[6] - rows[k, C_RATIO]) <= 5.1e-5
+        assert abs(nsuc / (k + 1) - rows[k, C_PSUC]) <= 5.1e-5
+        assert abs(tr[7] - rows[k, C_DPOS]) <= 5.1e-6 and abs(tr[8] - rows[k, C_DHOEK]) <= 5.1e-6
+        if acc[k]:
+            assert np.abs(np.concatenate([com[i1 - 1], hoek[i1 - 1]]) - moved[k]).max() < 5e-13
+            cur[i1 - 1] = np.concatenate([com[i1 - 1], hoek[i1 - 1]])
+    assert unresolved <= 10
+    # `Final energy (LJ)` prints TOTENG_OLD (MonteCarlo.F90:437): the energy the last step started from
+    assert abs(ch.stats()["toteng_old"] - float(t["final_energy"])) <= 2 * PRINT11 * abs(float(t["final_energy"]))
+
+
+def test_rng_stream_is_documented_xoshiro():
+    """u = (xoshiro256**(splitmix64(seed)) >> 11) * 2^-53; first outputs for seed 1 written out in python."""
+    M = (1 << 64) - 1
+
+    def splitmix(z):
+        z = (z + 0x9E3779B97F4A7C15) & M
+        x = z
+        x = ((x ^ (x >> 30)) * 0xBF58476D1CE4E5B9) & M
+        x = ((x ^ (x >> 27)) * 0x94D049BB133111EB) & M
+        return z, x ^ (x >> 31)
+
+    def rotl(x, k):
+        return ((x << k) | (x >> (64 - k))) & M
+
+    z, s = 1, []
+    for _ in range(4):
+        z, v = splitmix(z)
+        s.append(v)
+    st = ol.rng_seed(1)
+    assert [int(v) for v in st] == s
+    got = ol.rng_uniforms(st, 5)
+    for g in got:
+        r = (rotl((s[1] * 5) & M, 7) * 9) & M
+        t = (s[1] << 17) & M
+        s[2] ^= s[0]; s[3] ^= s[1]; s[1] ^= s[2]; s[0] ^= s[3]; s[2] ^= t; s[3] = rotl(s[3], 45)
+        assert g == (r >> 11) * 2.0 ** -53 and 0.0 <= g < 1.0
