@@ -1,0 +1,146 @@
+/* mcb200.h — C ABI of libmcb200.so: the classical LJ(+Coulomb) trial-move energy path of
+ * MatthijsLasure/MonteCarlo, rebuilt as fp64 CUDA for B200 (sm_100a).
+ *
+ * The reference has no FFI: its hot path is two internal procedures of the main program
+ * (calculateLJ, calcEnergy) plus module LennardJones, sharing state by host association.  This header is
+ * the boundary a Fortran driver binds with ISO_C_BINDING instead; every entry point
+ * names the reference code it stands in for (paths relative to the reference root).
+ *
+ * Conventions
+ *   - all functions return 0 on success, > 0 for an argument error, < 0 for a CUDA error;
+ *     mcb_last_error() gives the text.  The library never calls exit() and never clamps energies in the
+ *     single-step entry points (Inf/NaN are returned as values, as the reference's functions do).
+ *   - arrays of the reference's TYPE(vector) (MC_lib/vector_class.f90:18-20) are double[n][3], i.e. what
+ *     c_loc(arr) points at; molecule indices are 1-based like RSOLV.
+ *   - BOXL is HALF the box side (MonteCarlo.F90:296 BOXL2 = 2*BOXL).
+ *   - a handle is bound to one GPU and is not thread-safe; host buffers are the caller's.
+ *   - there is no CPU fallback: without a CUDA device mcb_create fails.
+ */
+#ifndef MCB200_H
+#define MCB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MCB_MAX_SITES 4 /* interacting sites per solvent molecule (DMSO: S, C, C, O; H is skipped) */
+
+typedef struct mcb_handle mcb_t;
+
+/* What calculateLJ reads besides the per-chain state (MonteCarlo.F90:306-310, :792-828). */
+typedef struct {
+    int n_mol;              /* NCOM */
+    int n_sites;            /* non-H atoms of the solvent molecule, 1..MCB_MAX_SITES (LennardJones.f90:66,68) */
+    int n_sol;              /* NSOL, may be 0 */
+    int n_chains;           /* independent copies of the box held on this GPU */
+    int device;             /* CUDA ordinal; -1 = the current device */
+    int quirk_31;           /* 1 = keep `IF (RSOLV .EQ. 31) RSOLV = 30` (MonteCarlo.F90:698) in mcb_run_steps */
+    int matrix_mode;        /* 0 auto, 1 force the pair matrix into global memory (never shared memory) */
+    int reserved;
+    double boxl;            /* half side, Angstrom */
+    double cutoff;          /* centre-of-mass cutoff, 7.0 in the reference (MonteCarlo.F90:812) */
+    double conv;            /* factor on the Coulomb sum; the reference's value is exactly 0.0 (LennardJones.f90:57) */
+    const double *site_rel; /* [n_sites][3] molecule-frame coordinates (rows of DMSO.txt with symbol != H) */
+    const double *site_tab; /* [n_sites][3] = (q, epsilon, sigma), ASSOSIATE_DMSO (LennardJones.f90:192-219) */
+} mcb_params;
+
+/* Per-chain Metropolis parameters: the driver's TEMPERATURE, DPOSMAX, ... (MonteCarlo.F90:33-47, :219-222). */
+typedef struct {
+    double temperature;
+    double dposmax, dposmin;
+    double dhoekmax, dhoekmin;  /* radians (the driver multiplies the config values by PI, :219-220) */
+    double padj;
+    int nadj;                   /* LJ_NADJ */
+    int reserved;
+    int64_t start_prod;         /* first step that counts for the production average (:222, :749) */
+} mcb_mc_params;
+
+/* Counters of one chain: NSUC, NACCEPT, PRODUCTION, PROD_ACC, TOTENG, ... (MonteCarlo.F90:36-44, :98-101). */
+typedef struct {
+    double toteng;          /* energy of the current (accepted) configuration */
+    double dposmax, dhoekmax;
+    double production;      /* sum of TOTENG over accepted steps >= start_prod (:749-752) */
+    double sum_e, sum_e2;   /* sum of the current energy and its square over every step >= start_prod */
+    double ratio;           /* REAL(NACCEPT)/REAL(NADJ) as of the last step (:758) */
+    double last_delta;      /* TOTENG - TOTENG_OLD of the last trial */
+    int64_t step;           /* steps done (UNICORN) */
+    int64_t nsuc;           /* accepted steps */
+    int64_t naccept;        /* accepted steps in the current adaptation window */
+    int64_t prod_acc;
+    int64_t n_clamped;      /* trial energies that were Inf/NaN and were clamped (:421-428) */
+    int64_t sitepairs;      /* LJ_FORMULA evaluations of trial states (the unit of the throughput metric) */
+    int64_t uniforms_used;
+    int64_t n_stat;         /* number of terms in sum_e / sum_e2 */
+} mcb_chain_stats;
+
+/* ---- life cycle --------------------------------------------------------------------------------- */
+/* replaces: the ALLOCATEs and table set-up at MonteCarlo.F90:306-322 */
+int mcb_create(mcb_t **out, const mcb_params *p);
+int mcb_destroy(mcb_t *h);
+const char *mcb_last_error(const mcb_t *h); /* h may be NULL: error of the last failed mcb_create */
+/* launch everything on this cudaStream_t (default: the legacy default stream) */
+int mcb_set_stream(mcb_t *h, void *cuda_stream);
+/* kernels launched by this handle so far */
+int64_t mcb_launch_count(const mcb_t *h);
+
+/* ---- state --------------------------------------------------------------------------------------- */
+/* replaces: SOLUTE and TABLE_SOL as read/associated at MonteCarlo.F90:1103-1114, LennardJones.f90:224-248
+ * (+ CHELPG charges, MonteCarlo.F90:353).  solute [c][n_sol][3], sol_tab [c][n_sol][3] = (q, eps, sigma);
+ * with broadcast != 0 one copy ([n_sol][3]) is given to all nchains chains. */
+int mcb_set_solute(mcb_t *h, int chain0, int nchains, const double *solute, const double *sol_tab, int broadcast);
+/* replaces: CoM / HOEK as read by read_norm (MonteCarlo.F90:1097-1099).  com, hoek [c][n_mol][3].
+ * Invalidates the cached energies of those chains until mcb_total_energy is called. */
+int mcb_set_chain_state(mcb_t *h, int chain0, int nchains, const double *com, const double *hoek, int broadcast);
+/* for the driver's dump / backup / result writers (MonteCarlo.F90:1009-1046, :587-611) */
+int mcb_get_chain_state(mcb_t *h, int chain0, int nchains, double *com, double *hoek);
+
+/* ---- energies ------------------------------------------------------------------------------------ */
+/* replaces: the start-up recompute `DO I=1,NCOM: CALL calculateLJ(I)` + calcEnergy (MonteCarlo.F90:357-364).
+ * Rebuilds the rotated-site cache, the pair matrix and ENERGY(:) of each chain.  Outputs (any may be NULL):
+ * toteng[c], e_solute_sum[c] = sum_i ENERGY(i), pairs_in_cutoff[c] = unordered CoM pairs inside the cutoff. */
+int mcb_total_energy(mcb_t *h, int chain0, int nchains, double *toteng, double *e_solute_sum,
+                     int64_t *pairs_in_cutoff);
+/* replaces: the `solventsolvent` dump (MonteCarlo.F90:372-376): ss [n_mol][n_mol], energy [n_mol] */
+int mcb_get_matrix(mcb_t *h, int chain, double *ss, double *energy);
+/* replaces: CALL calculateLJ(I) read-only (MonteCarlo.F90:792-828): row I of the pair matrix recomputed from
+ * the current coordinates with I as MOL1, and ENERGY(I).  i is 1-based. */
+int mcb_row_energy(mcb_t *h, int chain, int i, double *ss_row, double *e_i);
+
+/* ---- single-step mode: the driver keeps MCINIT / METROPOLIS (RNG, accept/reject) ------------------- */
+/* replaces: CALL calculateLJ(RSOLV) + calcEnergy for the trial state (MonteCarlo.F90:411-414), for the
+ * first nchains chains at once.  rsolv[c] 1-based; new_com, new_hoek [c][3] = the molecule after MCINIT's
+ * move and wrap (:699-712).  d_e[c] = TOTENG_trial - TOTENG_current, e_new[c] = TOTENG_trial. */
+int mcb_trial_delta(mcb_t *h, int nchains, const int *rsolv, const double *new_com, const double *new_hoek,
+                    double *d_e, double *e_new);
+/* replaces: the keep-or-roll-back at MonteCarlo.F90:779-786: accept[c] != 0 makes the pending trial of
+ * chain c current; 0 discards it. */
+int mcb_commit(mcb_t *h, int nchains, const unsigned char *accept);
+
+/* ---- batched mode: MCINIT + calculateLJ + calcEnergy + METROPOLIS looped on the GPU ----------------- */
+int mcb_set_mc_params(mcb_t *h, int chain0, int nchains, const mcb_mc_params *p, int broadcast);
+/* Uniform stream used when mcb_run_steps gets no buffer:  key = mix(seed + G), u_n = (mix(key + (n+1)*G) >> 11) * 2^-53,
+ * G = 0x9E3779B97F4A7C15, mix = splitmix64's finaliser; n counts the uniforms the chain has consumed.
+ * (The reference's own RNG is the compiler's RANDOM_NUMBER seeded from /dev/urandom, MC_lib/randgen.f90:15-40,
+ * so there is no reference stream to reproduce; a driver that wants its own stream passes a buffer.) */
+int mcb_seed_chains(mcb_t *h, int chain0, int nchains, const uint64_t *seeds);
+/* replaces: loop_LJ (MonteCarlo.F90:406-433) for nsteps steps of every chain.  uniforms: NULL (built-in
+ * stream) or host [n_chains][cap] doubles in [0,1): each step consumes 7 (MCINIT :697-700, lib.f90:115-130)
+ * plus 1 only when METROPOLIS draws (:739).  A chain stops early when fewer than 8 remain; consumed[c]
+ * (may be NULL) receives how many it used, steps_done[c] (may be NULL) how many steps it made. */
+int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, int64_t cap, int64_t *consumed,
+                  int64_t *steps_done);
+int mcb_get_stats(mcb_t *h, int chain0, int nchains, mcb_chain_stats *out);
+/* zero the counters (step, nsuc, production, ...) but keep coordinates, energies and step sizes */
+int mcb_reset_stats(mcb_t *h, int chain0, int nchains);
+
+/* ---- measurement ---------------------------------------------------------------------------------- */
+/* Independent DFMA chains on every SM for about `ms` milliseconds: the fp64 peak that the roofline
+ * fractions in bench.py are quoted against (MEASURED_PEAKS.json has no fp64 entry). */
+int mcb_measure_fp64_peak(int device, double ms, double *tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

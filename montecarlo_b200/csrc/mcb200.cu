@@ -1,0 +1,567 @@
+// mcb200.cu — host side of libmcb200.so: the C ABI declared in include/mcb200.h.
+//
+// Owns the device memory of one handle (per-chain images in HBM, optional global pair matrices, per-chain
+// scalars, scratch), packs the caller's AoS TYPE(vector) arrays into the SoA planes the kernels read, and
+// launches the kernels of mcb_kernels.cuh on the handle's stream.  There is no CPU path: every entry point
+// that computes something launches a kernel or fails.
+#include "../../include/mcb200.h"
+#include "mcb_kernels.cuh"
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace mcb;
+
+struct mcb_handle {
+    mcb_params prm{};
+    Geo g{};
+    SiteRel rel{};
+    int n_chains = 0, device = 0, n_sites = 0;
+    bool coul = false, can_step = false, dirty = true;
+    cudaStream_t stream = nullptr;
+    double *images = nullptr, *matg = nullptr, *work = nullptr;
+    ChainCtl *ctl = nullptr;
+    // scratch for entry-point inputs/outputs
+    int *d_rsolv = nullptr; double *d_vec = nullptr; double *d_out = nullptr; long long *d_ll = nullptr;
+    unsigned char *d_acc = nullptr; double *d_ubuf = nullptr; size_t ubuf_cap = 0;
+    double *pin = nullptr; size_t pin_doubles = 0;   // pinned staging
+    std::vector<double> site_tab;                     // [4][3] padded
+    std::vector<double> tab0AB, tab0Q;                // type-0 tables
+    long long launches = 0;
+    size_t smem_bytes = 0;
+    std::string err;
+};
+
+static std::string g_create_err;
+
+#define CK(h, call)                                                                                   \
+    do {                                                                                              \
+        cudaError_t e_ = (call);                                                                      \
+        if (e_ != cudaSuccess) {                                                                      \
+            (h)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                            \
+            return -(int)e_;                                                                          \
+        }                                                                                             \
+    } while (0)
+
+static int arg_err(mcb_t *h, const char *msg) { h->err = msg; return 1; }
+
+static size_t round_up(size_t v, size_t m) { return (v + m - 1) / m * m; }
+
+// largest x with sqrt(x) <= cutoff: `r2 > x` then decides exactly like `sqrt(r2) > cutoff` (MonteCarlo.F90:812)
+static double exact_cut2(double cutoff)
+{
+    double x = cutoff * cutoff;
+    while (std::sqrt(x) > cutoff) x = std::nextafter(x, 0.0);
+    while (std::sqrt(std::nextafter(x, INFINITY)) <= cutoff) x = std::nextafter(x, INFINITY);
+    return x;
+}
+
+// (A, B, QQ) of one site pair: LJ_FORMULA's E = sqrt(E1*E2), S = (S1+S2)/2 (LennardJones.f90:173-174)
+static void pair_consts(const double *ta, const double *tb, double conv, double &A, double &B, double &Q)
+{
+    long double e = sqrtl((long double)ta[1] * tb[1]);
+    long double s = ((long double)ta[2] + tb[2]) / 2.0L;
+    long double s2 = s * s, s6 = s2 * s2 * s2;
+    A = (double)(4.0L * e * s6 * s6);
+    B = (double)(4.0L * e * s6);
+    Q = (double)((long double)ta[0] * tb[0] * conv);
+}
+
+static void setup_geo(mcb_handle *h)
+{
+    const mcb_params &p = h->prm;
+    Geo &g = h->g;
+    g.N = p.n_mol; g.Np = (int)round_up(p.n_mol, 4); g.nsol = p.n_sol; g.nsolp = (p.n_sol + 3) / 4;
+    g.MS = (g.N % 2) ? g.N : g.N + 1;
+    g.o_com = 0; g.o_hoek = 3 * g.Np; g.o_energy = 6 * g.Np; g.o_sites = 7 * g.Np;
+    g.o_tabAB = g.o_sites + SITE_DOUBLES * (g.N + g.nsolp);
+    g.o_tabQ = g.o_tabAB + (1 + g.nsolp) * 32;
+    int end_tab = g.o_tabQ + (1 + g.nsolp) * 16;
+    g.o_mat = end_tab;
+    g.o_newrow = 0; g.o_list = g.Np; g.o_pend = g.Np + g.Np / 2;
+    g.work_doubles = (int)round_up(g.o_pend + (sizeof(Pending) + 7) / 8, 2);
+    size_t with_mat = round_up((size_t)end_tab + (size_t)g.N * g.MS, 2);
+    // the matrix rides in shared memory while a chain's footprint leaves room for >= 7 chains per SM
+    bool mat_smem = p.matrix_mode != 1 && (with_mat + g.work_doubles) * 8 <= 32 * 1024;
+    g.mat_in_image = mat_smem ? 1 : 0;
+    g.image_doubles = (int)(mat_smem ? with_mat : (size_t)end_tab);
+    g.stage_doubles = g.image_doubles;
+    g.quirk31 = p.quirk_31;
+    g.boxl = p.boxl; g.boxl2 = p.boxl * 2.0; g.inv_boxl = 1.0 / p.boxl; g.cut2 = exact_cut2(p.cutoff); g.conv = p.conv;
+    h->smem_bytes = ((size_t)g.stage_doubles + g.work_doubles) * 8;
+    h->can_step = h->smem_bytes <= 227 * 1024;
+}
+
+extern "C" const char *mcb_last_error(const mcb_t *h) { return h ? h->err.c_str() : g_create_err.c_str(); }
+
+extern "C" int mcb_destroy(mcb_t *h)
+{
+    if (!h) return 0;
+    cudaSetDevice(h->device);
+    cudaFree(h->images); cudaFree(h->matg); cudaFree(h->work); cudaFree(h->ctl);
+    cudaFree(h->d_rsolv); cudaFree(h->d_vec); cudaFree(h->d_out); cudaFree(h->d_ll); cudaFree(h->d_acc);
+    cudaFree(h->d_ubuf);
+    if (h->pin) cudaFreeHost(h->pin);
+    delete h;
+    return 0;
+}
+
+template <typename K>
+static int set_smem_attr(mcb_handle *h, K kernel)
+{
+    if (h->smem_bytes > 48 * 1024)
+        CK(h, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
+    return 0;
+}
+
+extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
+{
+    if (!out || !p) { g_create_err = "mcb_create: null argument"; return 1; }
+    *out = nullptr;
+    if (p->n_mol < 1 || p->n_chains < 1 || p->n_sites < 1 || p->n_sites > MCB_MAX_SITES || p->n_sol < 0 ||
+        !(p->boxl > 0.0) || !(p->cutoff > 0.0) || !p->site_rel || !p->site_tab) {
+        g_create_err = "mcb_create: bad parameter (n_mol, n_chains >= 1; 1 <= n_sites <= 4; boxl, cutoff > 0)";
+        return 1;
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        g_create_err = std::string("mcb_create: no CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e);
+        return -(int)(e != cudaSuccess ? e : cudaErrorNoDevice);
+    }
+    mcb_handle *h = new mcb_handle;
+    h->prm = *p;
+    h->n_chains = p->n_chains; h->n_sites = p->n_sites; h->coul = p->conv != 0.0;
+    if (p->device >= 0) h->device = p->device; else cudaGetDevice(&h->device);
+    auto fail = [&](int rc) { g_create_err = h->err; mcb_destroy(h); return rc; };
+#define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { h->err = std::string(#call) + ": " + cudaGetErrorString(e_); return fail(-(int)e_); } } while (0)
+    CKC(cudaSetDevice(h->device));
+    setup_geo(h);
+    const Geo &g = h->g;
+    // site tables, padded to 4 sites with parameter-free sites (they contribute exactly 0)
+    h->site_tab.assign(12, 0.0);
+    memset(&h->rel, 0, sizeof(h->rel));
+    h->rel.n_sites = p->n_sites;
+    for (int a = 0; a < p->n_sites; ++a)
+        for (int k = 0; k < 3; ++k) { h->rel.r[3 * a + k] = p->site_rel[3 * a + k]; h->site_tab[3 * a + k] = p->site_tab[3 * a + k]; }
+    for (int a = p->n_sites; a < 4; ++a) { h->rel.r[3 * a] = 1.0e4 + 7.0 * a; h->rel.r[3 * a + 1] = 2.0e4; h->rel.r[3 * a + 2] = 3.0e4; }
+    h->tab0AB.assign(32, 0.0); h->tab0Q.assign(16, 0.0);
+    for (int a = 0; a < p->n_sites; ++a)
+        for (int b = 0; b < p->n_sites; ++b) {
+            double A, B, Q;
+            pair_consts(&h->site_tab[3 * a], &h->site_tab[3 * b], p->conv, A, B, Q);
+            h->tab0AB[(a * 4 + b) * 2] = A; h->tab0AB[(a * 4 + b) * 2 + 1] = B; h->tab0Q[a * 4 + b] = Q;
+        }
+    const size_t nc = (size_t)h->n_chains;
+    CKC(cudaMalloc(&h->images, nc * g.image_doubles * sizeof(double)));
+    CKC(cudaMemset(h->images, 0, nc * g.image_doubles * sizeof(double)));
+    if (!g.mat_in_image) {
+        size_t bytes = nc * (size_t)g.N * g.MS * sizeof(double);
+        size_t free_b = 0, total_b = 0;
+        CKC(cudaMemGetInfo(&free_b, &total_b));
+        if (bytes > free_b / 2) { h->err = "mcb_create: pair matrices do not fit in device memory (n_chains * n_mol^2 too large)"; return fail(2); }
+        CKC(cudaMalloc(&h->matg, bytes));
+        CKC(cudaMemset(h->matg, 0, bytes));
+    }
+    CKC(cudaMalloc(&h->work, nc * g.work_doubles * sizeof(double)));
+    CKC(cudaMemset(h->work, 0, nc * g.work_doubles * sizeof(double)));
+    CKC(cudaMalloc(&h->ctl, nc * sizeof(ChainCtl)));
+    CKC(cudaMalloc(&h->d_rsolv, nc * sizeof(int)));
+    CKC(cudaMalloc(&h->d_vec, nc * 6 * sizeof(double)));
+    CKC(cudaMalloc(&h->d_out, nc * 3 * sizeof(double)));
+    CKC(cudaMalloc(&h->d_ll, nc * 2 * sizeof(long long)));
+    CKC(cudaMalloc(&h->d_acc, nc));
+    h->pin_doubles = nc * (size_t)std::max(6 * g.Np, g.image_doubles - g.o_sites - SITE_DOUBLES * g.N) + 64;
+    CKC(cudaMallocHost(&h->pin, h->pin_doubles * sizeof(double)));
+    // default Metropolis parameters = Tools/files/config0.ini:4-15; chain c is seeded with c+1
+    std::vector<ChainCtl> ctl(nc);
+    for (size_t c = 0; c < nc; ++c) {
+        ChainCtl &s = ctl[c];
+        memset(&s, 0, sizeof(s));
+        s.temperature = 300.0; s.dposmax = 0.30; s.dposmin = 1e-10; s.dhoekmax = 0.16 * PI_D; s.dhoekmin = 1e-10 * PI_D;
+        s.padj = 0.05; s.nadj = 100; s.start_prod = 0;
+        unsigned long long x = (unsigned long long)(c + 1) + 0x9E3779B97F4A7C15ULL;
+        x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL; x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL; x ^= x >> 31;
+        s.rng_key = x; s.rng_n = 0;
+    }
+    CKC(cudaMemcpy(h->ctl, ctl.data(), nc * sizeof(ChainCtl), cudaMemcpyHostToDevice));
+    if (h->can_step) {
+        int rc = 0;
+        rc |= set_smem_attr(h, k_run_steps<false, false, false>); rc |= set_smem_attr(h, k_run_steps<false, false, true>);
+        rc |= set_smem_attr(h, k_run_steps<false, true, false>);  rc |= set_smem_attr(h, k_run_steps<false, true, true>);
+        rc |= set_smem_attr(h, k_run_steps<true, false, false>);  rc |= set_smem_attr(h, k_run_steps<true, false, true>);
+        rc |= set_smem_attr(h, k_run_steps<true, true, false>);   rc |= set_smem_attr(h, k_run_steps<true, true, true>);
+        if (rc) return fail(rc);
+    }
+#undef CKC
+    *out = h;
+    // an empty solute section still needs the type-0 table in every image
+    return mcb_set_solute(h, 0, h->n_chains, nullptr, nullptr, 1);
+}
+
+extern "C" int mcb_set_stream(mcb_t *h, void *cuda_stream) { if (!h) return 1; h->stream = (cudaStream_t)cuda_stream; return 0; }
+extern "C" int64_t mcb_launch_count(const mcb_t *h) { return h ? h->launches : 0; }
+
+// ------------------------------------------------------------------------------------------------ state
+static int check_range(mcb_t *h, int chain0, int nchains)
+{
+    if (!h) return 1;
+    if (chain0 < 0 || nchains < 1 || chain0 + nchains > h->n_chains) return arg_err(h, "chain range outside [0, n_chains)");
+    return 0;
+}
+
+extern "C" int mcb_set_solute(mcb_t *h, int chain0, int nchains, const double *solute, const double *sol_tab, int broadcast)
+{
+    if (int rc = check_range(h, chain0, nchains)) return rc;
+    if ((solute == nullptr) != (sol_tab == nullptr)) return arg_err(h, "mcb_set_solute: solute and sol_tab must both be given");
+    const Geo &g = h->g;
+    CK(h, cudaSetDevice(h->device));
+    // the tail of an image: [solute pseudo-molecule sites][tabAB][tabQ], contiguous
+    const int tail0 = g.o_sites + SITE_DOUBLES * g.N, tail = g.o_mat - tail0;
+    if ((size_t)nchains * tail > h->pin_doubles) return arg_err(h, "internal: staging buffer too small");
+    for (int c = 0; c < nchains; ++c) {
+        double *t = h->pin + (size_t)c * tail;
+        double *sites = t, *ab = t + (g.o_tabAB - tail0), *tq = t + (g.o_tabQ - tail0);
+        const double *xyz = solute ? solute + (broadcast ? 0 : (size_t)c * g.nsol * 3) : nullptr;
+        const double *tb = sol_tab ? sol_tab + (broadcast ? 0 : (size_t)c * g.nsol * 3) : nullptr;
+        memset(t, 0, sizeof(double) * tail);
+        memcpy(ab, h->tab0AB.data(), 32 * sizeof(double));
+        memcpy(tq, h->tab0Q.data(), 16 * sizeof(double));
+        for (int p = 0; p < g.nsolp; ++p)
+            for (int b = 0; b < 4; ++b) {
+                int atom = 4 * p + b;
+                double *s = sites + SITE_DOUBLES * p + 3 * b;
+                if (xyz && atom < g.nsol) {
+                    s[0] = xyz[3 * atom]; s[1] = xyz[3 * atom + 1]; s[2] = xyz[3 * atom + 2];
+                    for (int a = 0; a < h->n_sites; ++a) {
+                        double A, B, Q;
+                        pair_consts(&h->site_tab[3 * a], tb + 3 * atom, h->prm.conv, A, B, Q);
+                        ab[(((1 + p) * 4 + a) * 4 + b) * 2] = A; ab[(((1 + p) * 4 + a) * 4 + b) * 2 + 1] = B;
+                        tq[((1 + p) * 4 + a) * 4 + b] = Q;
+                    }
+                } else {   // padding atom: no parameters, parked far outside any box
+                    s[0] = 4.0e4 + 11.0 * atom; s[1] = 5.0e4; s[2] = 6.0e4;
+                }
+            }
+    }
+    CK(h, cudaMemcpy2DAsync(h->images + (size_t)chain0 * g.image_doubles + tail0, (size_t)g.image_doubles * 8, h->pin,
+                            (size_t)tail * 8, (size_t)tail * 8, nchains, cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    h->dirty = true;
+    return 0;
+}
+
+extern "C" int mcb_set_chain_state(mcb_t *h, int chain0, int nchains, const double *com, const double *hoek, int broadcast)
+{
+    if (int rc = check_range(h, chain0, nchains)) return rc;
+    if (!com || !hoek) return arg_err(h, "mcb_set_chain_state: null array");
+    const Geo &g = h->g;
+    CK(h, cudaSetDevice(h->device));
+    const int w = 6 * g.Np;   // com planes + hoek planes are adjacent at the head of the image
+    for (int c = 0; c < nchains; ++c) {
+        double *t = h->pin + (size_t)c * w;
+        const double *cc = com + (broadcast ? 0 : (size_t)c * g.N * 3), *hh = hoek + (broadcast ? 0 : (size_t)c * g.N * 3);
+        if (broadcast && c > 0) { memcpy(t, h->pin, sizeof(double) * w); continue; }
+        memset(t, 0, sizeof(double) * w);
+        for (int j = 0; j < g.N; ++j)
+            for (int k = 0; k < 3; ++k) { t[k * g.Np + j] = cc[3 * j + k]; t[(3 + k) * g.Np + j] = hh[3 * j + k]; }
+    }
+    CK(h, cudaMemcpy2DAsync(h->images + (size_t)chain0 * g.image_doubles, (size_t)g.image_doubles * 8, h->pin, (size_t)w * 8,
+                            (size_t)w * 8, nchains, cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    h->dirty = true;
+    return 0;
+}
+
+extern "C" int mcb_get_chain_state(mcb_t *h, int chain0, int nchains, double *com, double *hoek)
+{
+    if (int rc = check_range(h, chain0, nchains)) return rc;
+    const Geo &g = h->g;
+    CK(h, cudaSetDevice(h->device));
+    const int w = 6 * g.Np;
+    CK(h, cudaMemcpy2DAsync(h->pin, (size_t)w * 8, h->images + (size_t)chain0 * g.image_doubles, (size_t)g.image_doubles * 8,
+                            (size_t)w * 8, nchains, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    for (int c = 0; c < nchains; ++c) {
+        const double *t = h->pin + (size_t)c * w;
+        for (int j = 0; j < g.N; ++j)
+            for (int k = 0; k < 3; ++k) {
+                if (com) com[((size_t)c * g.N + j) * 3 + k] = t[k * g.Np + j];
+                if (hoek) hoek[((size_t)c * g.N + j) * 3 + k] = t[(3 + k) * g.Np + j];
+            }
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ energies
+static int launch_prepare(mcb_t *h, int chain0, int nchains, double *d_tot, double *d_esol, long long *d_pairs)
+{
+    if (h->coul) k_prepare<true><<<nchains, 32, 0, h->stream>>>(h->g, h->rel, h->images, h->matg, h->work, h->ctl, chain0, d_tot, d_esol, d_pairs);
+    else k_prepare<false><<<nchains, 32, 0, h->stream>>>(h->g, h->rel, h->images, h->matg, h->work, h->ctl, chain0, d_tot, d_esol, d_pairs);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    return 0;
+}
+
+static int ensure_prepared(mcb_t *h)
+{
+    if (!h->dirty) return 0;
+    if (int rc = launch_prepare(h, 0, h->n_chains, nullptr, nullptr, nullptr)) return rc;
+    h->dirty = false;
+    return 0;
+}
+
+extern "C" int mcb_total_energy(mcb_t *h, int chain0, int nchains, double *toteng, double *e_solute_sum, int64_t *pairs_in_cutoff)
+{
+    if (int rc = check_range(h, chain0, nchains)) return rc;
+    CK(h, cudaSetDevice(h->device));
+    double *d_tot = h->d_out, *d_esol = h->d_out + h->n_chains;
+    if (int rc = launch_prepare(h, chain0, nchains, d_tot, d_esol, h->d_ll)) return rc;
+    std::vector<long long> pairs(nchains);
+    if (toteng) CK(h, cudaMemcpyAsync(toteng, d_tot, sizeof(double) * nchains, cudaMemcpyDeviceToHost, h->stream));
+    if (e_solute_sum) CK(h, cudaMemcpyAsync(e_solute_sum, d_esol, sizeof(double) * nchains, cudaMemcpyDeviceToHost, h->stream));
+    if (pairs_in_cutoff) CK(h, cudaMemcpyAsync(pairs.data(), h->d_ll, sizeof(long long) * nchains, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    if (pairs_in_cutoff) for (int c = 0; c < nchains; ++c) pairs_in_cutoff[c] = pairs[c];
+    if (chain0 == 0 && nchains == h->n_chains) h->dirty = false;
+    return 0;
+}
+
+extern "C" int mcb_get_matrix(mcb_t *h, int chain, double *ss, double *energy)
+{
+    if (int rc = check_range(h, chain, 1)) return rc;
+    if (int rc = ensure_prepared(h)) return rc;
+    const Geo &g = h->g;
+    const double *mat = g.mat_in_image ? h->images + (size_t)chain * g.image_doubles + g.o_mat : h->matg + (size_t)chain * g.N * g.MS;
+    if (ss) CK(h, cudaMemcpy2DAsync(ss, (size_t)g.N * 8, mat, (size_t)g.MS * 8, (size_t)g.N * 8, g.N, cudaMemcpyDeviceToHost, h->stream));
+    if (energy) CK(h, cudaMemcpyAsync(energy, h->images + (size_t)chain * g.image_doubles + g.o_energy, (size_t)g.N * 8, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+static int launch_trial(mcb_t *h, int chain0, int nchains, int read_only)
+{
+    double *d_com = h->d_vec, *d_hoek = h->d_vec + 3 * (size_t)h->n_chains;
+    double *d_dE = h->d_out, *d_en = h->d_out + h->n_chains;
+    if (h->coul) k_trial<true><<<nchains, 32, 0, h->stream>>>(h->g, h->rel, h->images, h->matg, h->work, h->ctl, chain0, h->d_rsolv, d_com, d_hoek, d_dE, d_en, read_only);
+    else k_trial<false><<<nchains, 32, 0, h->stream>>>(h->g, h->rel, h->images, h->matg, h->work, h->ctl, chain0, h->d_rsolv, d_com, d_hoek, d_dE, d_en, read_only);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    return 0;
+}
+
+extern "C" int mcb_trial_delta(mcb_t *h, int nchains, const int *rsolv, const double *new_com, const double *new_hoek,
+                               double *d_e, double *e_new)
+{
+    if (int rc = check_range(h, 0, nchains)) return rc;
+    if (!rsolv || !new_com || !new_hoek) return arg_err(h, "mcb_trial_delta: null array");
+    for (int c = 0; c < nchains; ++c)
+        if (rsolv[c] < 1 || rsolv[c] > h->g.N) return arg_err(h, "mcb_trial_delta: rsolv outside 1..n_mol");
+    CK(h, cudaSetDevice(h->device));
+    if (int rc = ensure_prepared(h)) return rc;
+    double *d_com = h->d_vec, *d_hoek = h->d_vec + 3 * (size_t)h->n_chains;
+    CK(h, cudaMemcpyAsync(h->d_rsolv, rsolv, sizeof(int) * nchains, cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaMemcpyAsync(d_com, new_com, sizeof(double) * 3 * nchains, cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaMemcpyAsync(d_hoek, new_hoek, sizeof(double) * 3 * nchains, cudaMemcpyHostToDevice, h->stream));
+    if (int rc = launch_trial(h, 0, nchains, 0)) return rc;
+    if (d_e) CK(h, cudaMemcpyAsync(d_e, h->d_out, sizeof(double) * nchains, cudaMemcpyDeviceToHost, h->stream));
+    if (e_new) CK(h, cudaMemcpyAsync(e_new, h->d_out + h->n_chains, sizeof(double) * nchains, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int mcb_commit(mcb_t *h, int nchains, const unsigned char *accept)
+{
+    if (int rc = check_range(h, 0, nchains)) return rc;
+    if (!accept) return arg_err(h, "mcb_commit: null array");
+    CK(h, cudaSetDevice(h->device));
+    CK(h, cudaMemcpyAsync(h->d_acc, accept, nchains, cudaMemcpyHostToDevice, h->stream));
+    k_commit<<<nchains, 32, 0, h->stream>>>(h->g, h->images, h->matg, h->work, h->ctl, h->d_acc);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int mcb_row_energy(mcb_t *h, int chain, int i, double *ss_row, double *e_i)
+{
+    if (int rc = check_range(h, chain, 1)) return rc;
+    if (i < 1 || i > h->g.N) return arg_err(h, "mcb_row_energy: i outside 1..n_mol");
+    CK(h, cudaSetDevice(h->device));
+    if (int rc = ensure_prepared(h)) return rc;
+    const Geo &g = h->g;
+    // a read-only "trial" that moves molecule i onto itself: new coordinates = current coordinates
+    std::vector<double> com((size_t)g.N * 3), hoek((size_t)g.N * 3);
+    if (int rc = mcb_get_chain_state(h, chain, 1, com.data(), hoek.data())) return rc;
+    double *d_com = h->d_vec, *d_hoek = h->d_vec + 3 * (size_t)h->n_chains;
+    CK(h, cudaMemcpyAsync(h->d_rsolv, &i, sizeof(int), cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaMemcpyAsync(d_com, &com[(size_t)(i - 1) * 3], sizeof(double) * 3, cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaMemcpyAsync(d_hoek, &hoek[(size_t)(i - 1) * 3], sizeof(double) * 3, cudaMemcpyHostToDevice, h->stream));
+    if (int rc = launch_trial(h, chain, 1, 1)) return rc;
+    const double *wk = h->work + (size_t)chain * g.work_doubles;
+    if (ss_row) CK(h, cudaMemcpyAsync(ss_row, wk + g.o_newrow, sizeof(double) * g.N, cudaMemcpyDeviceToHost, h->stream));
+    if (e_i) CK(h, cudaMemcpyAsync(e_i, reinterpret_cast<const char *>(wk + g.o_pend) + offsetof(Pending, e_sol), sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ batched mode
+static int edit_ctl(mcb_t *h, int chain0, int nchains, std::vector<ChainCtl> &ctl)
+{
+    ctl.resize(nchains);
+    CK(h, cudaSetDevice(h->device));
+    CK(h, cudaMemcpyAsync(ctl.data(), h->ctl + chain0, sizeof(ChainCtl) * nchains, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+static int store_ctl(mcb_t *h, int chain0, int nchains, const std::vector<ChainCtl> &ctl)
+{
+    CK(h, cudaMemcpyAsync(h->ctl + chain0, ctl.data(), sizeof(ChainCtl) * nchains, cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}
+
+extern "C" int mcb_set_mc_params(mcb_t *h, int chain0, int nchains, const mcb_mc_params *p, int broadcast)
+{
+    if (int rc = check_range(h, chain0, nchains)) return rc;
+    if (!p) return arg_err(h, "mcb_set_mc_params: null");
+    for (int c = 0; c < (broadcast ? 1 : nchains); ++c)
+        if (p[c].nadj < 1 || !(p[c].temperature > 0.0)) return arg_err(h, "mcb_set_mc_params: nadj >= 1 and temperature > 0 required");
+    std::vector<ChainCtl> ctl;
+    if (int rc = edit_ctl(h, chain0, nchains, ctl)) return rc;
+    for (int c = 0; c < nchains; ++c) {
+        const mcb_mc_params &q = p[broadcast ? 0 : c];
+        ChainCtl &s = ctl[c];
+        s.temperature = q.temperature; s.dposmax = q.dposmax; s.dposmin = q.dposmin; s.dhoekmax = q.dhoekmax;
+        s.dhoekmin = q.dhoekmin; s.padj = q.padj; s.nadj = q.nadj; s.start_prod = q.start_prod;
+    }
+    return store_ctl(h, chain0, nchains, ctl);
+}
+
+extern "C" int mcb_seed_chains(mcb_t *h, int chain0, int nchains, const uint64_t *seeds)
+{
+    if (int rc = check_range(h, chain0, nchains)) return rc;
+    if (!seeds) return arg_err(h, "mcb_seed_chains: null");
+    std::vector<ChainCtl> ctl;
+    if (int rc = edit_ctl(h, chain0, nchains, ctl)) return rc;
+    for (int c = 0; c < nchains; ++c) {
+        unsigned long long x = seeds[c] + 0x9E3779B97F4A7C15ULL;
+        x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL; x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL; x ^= x >> 31;
+        ctl[c].rng_key = x; ctl[c].rng_n = 0;
+    }
+    return store_ctl(h, chain0, nchains, ctl);
+}
+
+extern "C" int mcb_reset_stats(mcb_t *h, int chain0, int nchains)
+{
+    if (int rc = check_range(h, chain0, nchains)) return rc;
+    std::vector<ChainCtl> ctl;
+    if (int rc = edit_ctl(h, chain0, nchains, ctl)) return rc;
+    for (auto &s : ctl) {
+        s.production = s.sum_e = s.sum_e2 = s.ratio = s.last_delta = 0.0;
+        s.step = s.nsuc = s.naccept = s.prod_acc = s.nclamp = s.sitepairs = s.uused = s.nstat = 0;
+    }
+    return store_ctl(h, chain0, nchains, ctl);
+}
+
+extern "C" int mcb_get_stats(mcb_t *h, int chain0, int nchains, mcb_chain_stats *out)
+{
+    if (int rc = check_range(h, chain0, nchains)) return rc;
+    if (!out) return arg_err(h, "mcb_get_stats: null");
+    if (int rc = ensure_prepared(h)) return rc;
+    std::vector<ChainCtl> ctl;
+    if (int rc = edit_ctl(h, chain0, nchains, ctl)) return rc;
+    for (int c = 0; c < nchains; ++c) {
+        const ChainCtl &s = ctl[c];
+        mcb_chain_stats &o = out[c];
+        o.toteng = s.toteng; o.dposmax = s.dposmax; o.dhoekmax = s.dhoekmax; o.production = s.production;
+        o.sum_e = s.sum_e; o.sum_e2 = s.sum_e2; o.ratio = s.ratio; o.last_delta = s.last_delta;
+        o.step = s.step; o.nsuc = s.nsuc; o.naccept = s.naccept; o.prod_acc = s.prod_acc; o.n_clamped = s.nclamp;
+        o.sitepairs = s.sitepairs; o.uniforms_used = s.uused; o.n_stat = s.nstat;
+    }
+    return 0;
+}
+
+template <bool COUL, bool UBUF>
+static void launch_run(mcb_t *h, long long nsteps, long long cap, long long *d_consumed, long long *d_steps)
+{
+    if (h->g.mat_in_image)
+        k_run_steps<COUL, UBUF, true><<<h->n_chains, 32, h->smem_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, h->d_ubuf, cap, d_consumed, d_steps);
+    else
+        k_run_steps<COUL, UBUF, false><<<h->n_chains, 32, h->smem_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, h->d_ubuf, cap, d_consumed, d_steps);
+}
+
+extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, int64_t cap, int64_t *consumed, int64_t *steps_done)
+{
+    if (!h) return 1;
+    if (nsteps < 0) return arg_err(h, "mcb_run_steps: nsteps < 0");
+    if (!h->can_step) return arg_err(h, "mcb_run_steps: a chain of this size does not fit in shared memory (energy-only mode)");
+    if (uniforms && cap < 8) return arg_err(h, "mcb_run_steps: uniform buffer needs cap >= 8 per chain");
+    CK(h, cudaSetDevice(h->device));
+    if (int rc = ensure_prepared(h)) return rc;
+    const size_t nc = (size_t)h->n_chains;
+    if (uniforms) {
+        size_t need = nc * (size_t)cap;
+        if (need > h->ubuf_cap) {
+            cudaFree(h->d_ubuf); h->d_ubuf = nullptr; h->ubuf_cap = 0;
+            CK(h, cudaMalloc(&h->d_ubuf, need * sizeof(double)));
+            h->ubuf_cap = need;
+        }
+        CK(h, cudaMemcpyAsync(h->d_ubuf, uniforms, need * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    }
+    long long *d_consumed = h->d_ll, *d_steps = h->d_ll + nc;
+    if (uniforms) { if (h->coul) launch_run<true, true>(h, nsteps, cap, d_consumed, d_steps); else launch_run<false, true>(h, nsteps, cap, d_consumed, d_steps); }
+    else { if (h->coul) launch_run<true, false>(h, nsteps, 0, d_consumed, d_steps); else launch_run<false, false>(h, nsteps, 0, d_consumed, d_steps); }
+    h->launches++;
+    CK(h, cudaGetLastError());
+    std::vector<long long> tmp;
+    if (consumed || steps_done) {
+        tmp.resize(2 * nc);
+        CK(h, cudaMemcpyAsync(tmp.data(), h->d_ll, sizeof(long long) * 2 * nc, cudaMemcpyDeviceToHost, h->stream));
+    }
+    CK(h, cudaStreamSynchronize(h->stream));
+    for (size_t c = 0; c < nc && !tmp.empty(); ++c) {
+        if (consumed) consumed[c] = tmp[c];
+        if (steps_done) steps_done[c] = tmp[nc + c];
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ measurement
+extern "C" int mcb_measure_fp64_peak(int device, double ms, double *tflops)
+{
+    if (!tflops) return 1;
+    if (device >= 0 && cudaSetDevice(device) != cudaSuccess) return -1;
+    cudaDeviceProp prop;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) return -1;
+    const int blocks = prop.multiProcessorCount * 8, threads = 256;
+    double *out = nullptr;
+    if (cudaMalloc(&out, sizeof(double) * blocks * threads) != cudaSuccess) return -2;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    int iters = 2000;
+    double best = 0.0;
+    float t = 0.f;
+    for (int rep = 0; rep < 6; ++rep) {
+        cudaEventRecord(e0);
+        k_fp64_peak<<<blocks, threads>>>(out, iters);
+        cudaEventRecord(e1);
+        if (cudaEventSynchronize(e1) != cudaSuccess) { cudaFree(out); return -3; }
+        cudaEventElapsedTime(&t, e0, e1);
+        double flops = 2.0 * 8 * 16 * (double)iters * blocks * threads;
+        double tf = flops / (t * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+        if (t < ms) iters = (int)std::min(2.0e6, iters * std::max(1.5, ms / std::max(t, 0.01f)));
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(out);
+    *tflops = best;
+    return 0;
+}

@@ -613,39 +613,39 @@ int64_t mco_run_steps(mco_chain *c, int64_t nsteps, const double *uniforms, int6
 }
 
 /* ------------------------------------------------------------------ uniform stream */
-static inline uint64_t rotl64(uint64_t x, int k) { return (x << k) | (x >> (64 - k)); }
-
-void mco_rng_seed(uint64_t s[4], uint64_t seed)
+/* Counter-based stream (shared definition with include/mcb200.h, mcb_seed_chains):
+ *   G = 0x9E3779B97F4A7C15, mix = splitmix64 finaliser, key = mix(seed + G),
+ *   u_n = (mix(key + (n+1)*G) >> 11) * 2^-53 for n = 0, 1, 2, ...   state = {key, n}. */
+static inline uint64_t mix64(uint64_t x)
 {
-    uint64_t z = seed;
-    for (int i = 0; i < 4; ++i) { /* splitmix64 */
-        z += 0x9E3779B97F4A7C15ULL;
-        uint64_t x = z;
-        x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
-        x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
-        s[i] = x ^ (x >> 31);
-    }
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
 }
 
-double mco_rng_uniform(uint64_t s[4])
+void mco_rng_seed(uint64_t s[2], uint64_t seed)
 {
-    uint64_t result = rotl64(s[1] * 5, 7) * 9; /* xoshiro256** */
-    uint64_t t = s[1] << 17;
-    s[2] ^= s[0]; s[3] ^= s[1]; s[1] ^= s[2]; s[0] ^= s[3];
-    s[2] ^= t; s[3] = rotl64(s[3], 45);
-    return (double)(result >> 11) * 0x1.0p-53;
+    s[0] = mix64(seed + 0x9E3779B97F4A7C15ULL);
+    s[1] = 0;
 }
 
-int64_t mco_run_steps_rng(mco_chain *c, int64_t nsteps, uint64_t rng[4], double *trace)
+double mco_rng_uniform(uint64_t s[2])
+{
+    s[1] += 1;
+    uint64_t x = mix64(s[0] + s[1] * 0x9E3779B97F4A7C15ULL);
+    return (double)(x >> 11) * 0x1.0p-53;
+}
+
+int64_t mco_run_steps_rng(mco_chain *c, int64_t nsteps, uint64_t rng[2], double *trace)
 {
     double u[8];
     for (int64_t s = 0; s < nsteps; ++s) {
         for (int k = 0; k < 7; ++k) u[k] = mco_rng_uniform(rng);
         int i = mco_mcinit(c, u);
         /* the 8th uniform is drawn only when METROPOLIS needs it (MonteCarlo.F90:739) */
-        uint64_t save[4] = {rng[0], rng[1], rng[2], rng[3]};
+        uint64_t save = rng[1];
         u[7] = mco_rng_uniform(rng);
-        if (!finish_step(c, i, u + 7, trace ? trace + 10 * s : NULL)) memcpy(rng, save, sizeof(save));
+        if (!finish_step(c, i, u + 7, trace ? trace + 10 * s : NULL)) rng[1] = save;
     }
     return nsteps;
 }

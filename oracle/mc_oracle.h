@@ -82,18 +82,19 @@ int mco_step_given_move(mco_chain *c, int i, const double new_com[3], const doub
 /* nsteps steps fed from a uniform buffer; stops early (returns steps done) if the buffer runs out */
 int64_t mco_run_steps(mco_chain *c, int64_t nsteps, const double *uniforms, int64_t cap, int64_t *consumed,
                       double *trace /* [nsteps][10] or NULL */);
-/* nsteps steps fed from the built-in xoshiro256** stream (state advanced in place) */
-int64_t mco_run_steps_rng(mco_chain *c, int64_t nsteps, uint64_t rng[4], double *trace);
+/* nsteps steps fed from the built-in counter-based stream (state advanced in place) */
+int64_t mco_run_steps_rng(mco_chain *c, int64_t nsteps, uint64_t rng[2], double *trace);
 
 /* counters: {step, nsuc, naccept_window, prod_acc, n_clamped, sitepairs(lo), toteng, toteng_old, production,
  *            dposmax, dhoekmax} */
 void mco_get_stats(const mco_chain *c, double out[12]);
 
 /* ---- the documented uniform stream used when the driver does not supply uniforms ----
- * splitmix64(seed) x4 -> xoshiro256** ; u = (x >> 11) * 2^-53 in [0,1).  Not from the reference: its RNG is
- * the compiler's RANDOM_NUMBER seeded from /dev/urandom (MC_lib/randgen.f90:15-40), so no stream exists to match. */
-void mco_rng_seed(uint64_t state[4], uint64_t seed);
-double mco_rng_uniform(uint64_t state[4]);
+ * G = 0x9E3779B97F4A7C15, mix = splitmix64's finaliser, key = mix(seed + G),
+ * u_n = (mix(key + (n+1)*G) >> 11) * 2^-53 in [0,1); state = {key, n}.  Not from the reference: its RNG is the
+ * compiler's RANDOM_NUMBER seeded from /dev/urandom (MC_lib/randgen.f90:15-40), so no stream exists to match. */
+void mco_rng_seed(uint64_t state[2], uint64_t seed);
+double mco_rng_uniform(uint64_t state[2]);
 
 #ifdef __cplusplus
 }

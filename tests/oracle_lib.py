@@ -176,7 +176,7 @@ class OracleChain:
 
 
 def rng_seed(seed: int) -> np.ndarray:
-    s = np.zeros(4, dtype=np.uint64)
+    s = np.zeros(2, dtype=np.uint64)
     lib().mco_rng_seed(_ptr(s, _u64p), C.c_uint64(seed))
     return s
 

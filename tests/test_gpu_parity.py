@@ -1,0 +1,351 @@
+"""GPU: the CUDA path (through the C ABI) against the oracle and the reference-produced fixtures.
+
+Tolerances: BASELINE.json asks for 1e-10 relative on per-move dE and full-box energy; energies are compared
+at RTOL = 1e-10 relative to the energies involved, coordinates at 1e-12 absolute, counters exactly.
+"""
+import json
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from golden_util import GOLD, C_TOT, C_OLD, C_RSOLV, load_trace
+from montecarlo_b200 import boxio
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-10
+PRINT11 = 6e-11
+
+
+def _engine(system, n, **kw):
+    from montecarlo_b200.engine import LJEngine
+    return LJEngine(system, n, **kw)
+
+
+def _sys_for(system, box):
+    return boxio.System(**{**system.__dict__, "boxl": box.boxl, "solute": box.solute})
+
+
+def _close(a, b, scale=None, rtol=RTOL):
+    a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
+    s = np.maximum(np.abs(a), np.abs(b)) if scale is None else scale
+    return np.all(np.abs(a - b) <= rtol * s + 1e-300)
+
+
+def test_startup_energy_and_matrix(shipped):
+    box, system = shipped
+    g = np.load(GOLD / "ref_startup_k1.npz")
+    eng = _engine(system, box.n, n_chains=3)
+    eng.set_state(box.com, box.hoek)
+    tot, esol, pairs = eng.total_energy()
+    o = ol.OracleChain(system, box.com, box.hoek)
+    e = o.total_energy()
+    assert _close(tot, e) and np.all(pairs == 170)
+    assert np.all(np.abs(tot - float(g["initial_energy"])) <= PRINT11 * abs(e))   # the reference's printed value
+    ss, en = eng.matrix(1)
+    oss, oen = o.matrix()
+    assert np.array_equal(ss != 0, oss != 0) and np.array_equal(ss, ss.T)
+    assert _close(ss, oss, scale=np.abs(oss) + 1e-3) and _close(en, oen)
+    ref = g["matrix"]
+    nz = ref != 0
+    assert np.max(np.abs(ss[nz] - ref[nz]) / (np.abs(ref[nz]) + 1e-3)) < 1e-10
+    assert abs(esol[0] - oen.sum()) <= RTOL * abs(oen.sum())
+    # quad arbiter: the GPU is as close to the exact value as the fp64 restatement is
+    q = ol.OracleChain(system, box.com, box.hoek, quad=True).total_energy()
+    assert abs(tot[0] - q) <= 1e-12 * abs(q)
+
+
+@pytest.mark.parametrize("matrix_mode", [0, 1])
+def test_startup_replica_k2(shipped, matrix_mode):
+    box, system = shipped
+    g = np.load(GOLD / "ref_startup_k2.npz")
+    b2 = boxio.replicate(box, 2)
+    s2 = _sys_for(system, b2)
+    eng = _engine(s2, b2.n, n_chains=2, matrix_mode=matrix_mode)
+    eng.set_state(b2.com, b2.hoek)
+    tot, esol, pairs = eng.total_energy()
+    assert np.all(np.abs(tot - float(g["initial_energy"])) <= PRINT11 * abs(tot[0])) and np.all(pairs == 1360)
+    ss, _ = eng.matrix(0)
+    ref = g["matrix"]
+    assert np.array_equal(ss != 0, ref != 0)
+    nz = ref != 0
+    assert np.max(np.abs(ss[nz] - ref[nz]) / (np.abs(ref[nz]) + 1e-3)) < 1e-10
+
+
+def test_startup_replica_k5(shipped):
+    box, system = shipped
+    g = json.loads((GOLD / "ref_startup_k5.json").read_text())
+    b5 = boxio.replicate(box, 5)
+    eng = _engine(_sys_for(system, b5), b5.n, n_chains=1)
+    eng.set_state(b5.com, b5.hoek)
+    tot, esol, pairs = eng.total_energy()
+    assert abs(tot[0] - g["initial_energy"]) <= PRINT11 * abs(tot[0])
+    assert 2 * pairs[0] == g["nonzero"]
+    assert abs((tot[0] - esol[0]) - g["sum_upper"]) <= 1e-9 * abs(tot[0])
+
+
+def test_coulomb_path_when_conv_is_nonzero(shipped):
+    """The reference's CONV is 0 (LennardJones.f90:57); the kernel still carries q1 q2 / r * conv."""
+    box, system = shipped
+    charges = json.loads((GOLD / "ref_charges.json").read_text())["charges"]
+    tab = system.sol_tab.copy(); tab[:, 0] = charges
+    conv = ol.lib().mco_const_conv_intended()
+    s = boxio.System(**{**system.__dict__, "sol_tab": tab, "conv": conv})
+    eng = _engine(s, box.n, n_chains=1)
+    eng.set_state(box.com, box.hoek)
+    tot, _, _ = eng.total_energy()
+    o = ol.OracleChain(s, box.com, box.hoek)
+    e = o.total_energy()
+    assert abs(e - 2796.8745663) > 1.0            # the Coulomb term really contributes here
+    assert _close(tot[0], e)
+    ss, en = eng.matrix(0)
+    oss, oen = o.matrix()
+    assert _close(ss, oss, scale=np.abs(oss) + 1e-3) and _close(en, oen)
+    # and with conv = 0 the same charges change nothing (what the reference binary does, ref_charges.json)
+    s0 = boxio.System(**{**system.__dict__, "sol_tab": tab, "conv": 0.0})
+    eng0 = _engine(s0, box.n, n_chains=1)
+    eng0.set_state(box.com, box.hoek)
+    assert abs(eng0.total_energy()[0][0] - 2796.8745663) <= PRINT11 * 2796.87
+
+
+def test_row_energy_is_calculateLJ(shipped):
+    box, system = shipped
+    eng = _engine(system, box.n, n_chains=2)
+    eng.set_state(box.com, box.hoek)
+    o = ol.OracleChain(system, box.com, box.hoek)
+    for i in (1, 6, 17, 30):
+        row, ei = eng.row_energy(1, i)
+        _, orow, oei = o.row_energy(i - 1)
+        assert np.array_equal(row != 0, orow != 0)
+        assert _close(row, orow, scale=np.abs(orow) + 1e-3) and _close(ei, oei)
+
+
+def test_single_step_mode_replays_reference_trace(shipped):
+    """mcb_trial_delta / mcb_commit fed the trial moves the reference itself made (DUMP) and its decisions:
+    TOTENG of every trial against the reference's printed OUT rows and against the oracle."""
+    box, system = shipped
+    t = load_trace("ref_trace_10k.npz")
+    rows, moved, acc = t["out_rows"], t["moved"], t["accepted"]
+    nstep = 3000
+    eng = _engine(system, box.n, n_chains=1)
+    eng.set_state(box.com, box.hoek)
+    e0 = eng.total_energy()[0][0]
+    o = ol.OracleChain(system, box.com, box.hoek)
+    o.total_energy()
+    cur = e0
+    for k in range(nstep):
+        i1 = int(rows[k, C_RSOLV])
+        d_e, e_new = eng.trial_delta([i1], moved[k, 0:3], moved[k, 3:6])
+        _, tr = o.step_given_move(i1 - 1, moved[k, 0:3], moved[k, 3:6], 0.0 if acc[k] else 1.0)
+        scale = max(abs(tr[0]), abs(tr[1]))
+        assert abs(e_new[0] - tr[0]) <= RTOL * scale, (k, e_new[0], tr[0])
+        assert abs(d_e[0] - (tr[0] - tr[1])) <= RTOL * scale, (k, d_e[0], tr[0] - tr[1])
+        assert abs(e_new[0] - rows[k, C_TOT]) <= 2 * PRINT11 * max(abs(rows[k, C_TOT]), abs(rows[k, C_OLD])), k
+        eng.commit([1 if acc[k] else 0])
+        if acc[k]:
+            cur = e_new[0]
+    st = eng.stats()
+    assert abs(st["toteng"][0] - cur) <= RTOL * abs(cur)
+    # the tracked energy equals a fresh recompute of the final configuration
+    assert abs(eng.total_energy()[0][0] - cur) <= RTOL * abs(cur)
+    com, hoek = eng.get_state()
+    ocom, ohoek = o.get_state()
+    assert np.abs(com[0] - ocom).max() == 0.0 and np.abs(hoek[0] - ohoek).max() == 0.0
+
+
+def _compare_chain(st, c, so, com, hoek, o):
+    assert st["step"][c] == so["step"]
+    assert st["nsuc"][c] == so["nsuc"], (c, st["nsuc"][c], so["nsuc"])
+    assert st["naccept"][c] == so["naccept"] and st["prod_acc"][c] == so["prod_acc"]
+    assert st["sitepairs"][c] == so["sitepairs"]
+    assert abs(st["toteng"][c] - so["toteng"]) <= RTOL * abs(so["toteng"])
+    assert abs(st["production"][c] - so["production"]) <= RTOL * abs(so["production"]) + 1e-300
+    assert abs(st["dposmax"][c] - so["dposmax"]) <= 1e-15 and abs(st["dhoekmax"][c] - so["dhoekmax"]) <= 1e-15
+    ocom, ohoek = o.get_state()
+    assert np.abs(com[c] - ocom).max() <= 1e-12 and np.abs(hoek[c] - ohoek).max() <= 1e-12
+
+
+def test_batched_mode_with_driver_uniforms(shipped):
+    """mcb_run_steps fed a uniform buffer: same accept/reject sequence, state and counters as the oracle fed
+    the same buffer, for 10^4 steps per chain."""
+    box, system = shipped
+    nch, nsteps = 6, 10000
+    rng = np.random.default_rng(20261106)
+    u = rng.random((nch, 8 * nsteps))
+    eng = _engine(system, box.n, n_chains=nch)
+    eng.set_state(box.com, box.hoek)
+    eng.set_mc_params(start_prod=nsteps // 2)
+    consumed, steps = eng.run_steps(nsteps, u)
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    assert np.all(steps == nsteps)
+    for c in range(nch):
+        o = ol.OracleChain(system, box.com, box.hoek)
+        o.set_mc_params(start_prod=nsteps // 2)
+        o.total_energy()
+        done, used, _ = o.run_steps(nsteps, u[c], trace=False)
+        assert done == nsteps and used == consumed[c] == st["uniforms_used"][c]
+        _compare_chain(st, c, o.stats(), com, hoek, o)
+
+
+def test_batched_mode_builtin_stream_and_resume(shipped):
+    """Built-in counter stream, run in three launches (resume across launches must be seamless)."""
+    box, system = shipped
+    nch = 12
+    seeds = np.arange(1, nch + 1, dtype=np.uint64)
+    eng = _engine(system, box.n, n_chains=nch)
+    eng.set_state(box.com, box.hoek)
+    eng.seed(seeds)
+    eng.set_mc_params(nadj=50, padj=0.1, temperature=np.linspace(250.0, 400.0, nch))
+    for n in (1, 4999, 5000):
+        eng.run_steps(n)
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    temps = np.linspace(250.0, 400.0, nch)
+    for c in range(nch):
+        o = ol.OracleChain(system, box.com, box.hoek)
+        o.set_mc_params(temperature=temps[c], nadj=50, padj=0.1)
+        o.total_energy()
+        o.run_steps_rng(10000, ol.rng_seed(int(seeds[c])), trace=False)
+        _compare_chain(st, c, o.stats(), com, hoek, o)
+    # size-independent property: the running energy equals a fresh full-box recompute
+    fresh = eng.total_energy()[0]
+    assert np.all(np.abs(fresh - st["toteng"]) <= RTOL * np.abs(fresh))
+
+
+def test_uniform_buffer_runs_dry(shipped):
+    box, system = shipped
+    eng = _engine(system, box.n, n_chains=2)
+    eng.set_state(box.com, box.hoek)
+    u = np.random.default_rng(3).random((2, 100))
+    consumed, steps = eng.run_steps(50, u)
+    o = ol.OracleChain(system, box.com, box.hoek)
+    o.total_energy()
+    done, used, _ = o.run_steps(50, u[0], trace=False)
+    assert steps[0] == done and consumed[0] == used and done < 50 and np.all(consumed <= 100)
+
+
+@pytest.mark.parametrize("matrix_mode", [0, 1])
+def test_batched_mode_replica_box(shipped, matrix_mode):
+    """N = 240 (pair matrix in global memory), and the shipped box forced onto the global-matrix path."""
+    box, system = shipped
+    b = boxio.replicate(box, 2) if matrix_mode == 0 else box
+    s = _sys_for(system, b)
+    nch, nsteps = 3, 3000
+    eng = _engine(s, b.n, n_chains=nch, matrix_mode=matrix_mode)
+    eng.set_state(b.com, b.hoek)
+    eng.seed(np.array([11, 12, 13], dtype=np.uint64))
+    eng.run_steps(nsteps)
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    for c in range(nch):
+        o = ol.OracleChain(s, b.com, b.hoek)
+        o.total_energy()
+        o.run_steps_rng(nsteps, ol.rng_seed(11 + c), trace=False)
+        _compare_chain(st, c, o.stats(), com, hoek, o)
+
+
+def test_per_chain_solute_conformers(shipped):
+    """Config 4 shape: every chain sees its own solute coordinates."""
+    box, system = shipped
+    nch = 4
+    rng = np.random.default_rng(5)
+    sol = np.stack([system.solute + 0.05 * rng.standard_normal(system.solute.shape) for _ in range(nch)])
+    tabs = np.stack([system.sol_tab] * nch)
+    eng = _engine(system, box.n, n_chains=nch)
+    eng.set_solute(sol, tabs)
+    eng.set_state(box.com, box.hoek)
+    tot = eng.total_energy()[0]
+    eng.seed(np.arange(100, 100 + nch, dtype=np.uint64))
+    eng.run_steps(2000)
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    for c in range(nch):
+        o = ol.OracleChain(system, box.com, box.hoek, solute=sol[c])
+        assert abs(o.total_energy() - tot[c]) <= RTOL * abs(tot[c])
+        o.run_steps_rng(2000, ol.rng_seed(100 + c), trace=False)
+        _compare_chain(st, c, o.stats(), com, hoek, o)
+    assert len(set(np.round(tot, 6))) == nch
+
+
+def test_quirk_31_and_odd_sizes(shipped):
+    """N = 33 random box: molecule 31 is never picked, 30 twice as often (MonteCarlo.F90:698); N not a multiple of 4."""
+    box, system = shipped
+    rng = np.random.default_rng(9)
+    n = 33
+    boxl = 9.0
+    com = rng.uniform(-boxl, boxl, (n, 3)); hoek = rng.uniform(-np.pi, np.pi, (n, 3))
+    s = boxio.System(**{**system.__dict__, "boxl": boxl})
+    for quirk in (True, False):
+        eng = _engine(s, n, n_chains=2, quirk_31=quirk)
+        eng.set_state(com, hoek)
+        eng.seed(np.array([7, 8], dtype=np.uint64))
+        eng.run_steps(1500)
+        st = eng.stats()
+        c_, h_ = eng.get_state()
+        for c in range(2):
+            o = ol.OracleChain(s, com, hoek)
+            o.set_mc_params(quirk31=1 if quirk else 0)
+            o.total_energy()
+            o.run_steps_rng(1500, ol.rng_seed(7 + c), trace=False)
+            _compare_chain(st, c, o.stats(), c_, h_, o)
+        moved31 = np.abs(c_[:, 30] - com[30]).max() > 0
+        assert moved31 == (not quirk)
+
+
+def test_edge_cases(shipped):
+    box, system = shipped
+    # no solute at all
+    eng = _engine(system, box.n, n_chains=1, with_solute=False)
+    eng.set_state(box.com, box.hoek)
+    tot, esol, _ = eng.total_energy()
+    o = ol.OracleChain(system, box.com, box.hoek)
+    o.total_energy()
+    ss, en = o.matrix()
+    assert esol[0] == 0.0 and abs(tot[0] - np.triu(ss, 1).sum()) <= RTOL * abs(tot[0])
+    # a single molecule: only the solute term
+    eng1 = _engine(system, 1, n_chains=1)
+    eng1.set_state(box.com[:1], box.hoek[:1])
+    t1 = eng1.total_energy()[0][0]
+    assert abs(t1 - en[0]) <= RTOL * abs(en[0])
+    eng1.run_steps(10)
+    assert eng1.stats()["step"][0] == 10
+    # argument errors come back as status codes with a message, not as crashes
+    from montecarlo_b200.engine import McbError
+    with pytest.raises(McbError):
+        eng.trial_delta([0], box.com[0], box.hoek[0])
+    with pytest.raises(McbError):
+        eng.trial_delta([31], box.com[0], box.hoek[0])
+    with pytest.raises(McbError):
+        eng.run_steps(5, np.zeros((1, 4)))
+
+
+def test_full_size_properties(shipped):
+    """BASELINE config 2 size (1024 chains of the shipped box): determinism across identical seeds, independence
+    across different seeds, and running energy == fresh recompute for every chain."""
+    box, system = shipped
+    nch = 1024
+    eng = _engine(system, box.n, n_chains=nch)
+    eng.set_state(box.com, box.hoek)
+    seeds = np.arange(1, nch + 1, dtype=np.uint64)
+    seeds[512:] = seeds[:512]          # second half repeats the first
+    eng.seed(seeds)
+    eng.run_steps(2000)
+    st = eng.stats()
+    com, _ = eng.get_state()
+    assert np.array_equal(st["toteng"][:512], st["toteng"][512:]) and np.array_equal(com[:512], com[512:])
+    assert len(np.unique(st["toteng"][:512])) == 512
+    assert np.all(st["step"] == 2000) and np.all(st["n_clamped"] == 0)
+    fresh = eng.total_energy()[0]
+    assert np.all(np.abs(fresh - st["toteng"]) <= RTOL * np.abs(fresh))
+    o = ol.OracleChain(system, box.com, box.hoek)
+    o.total_energy()
+    o.run_steps_rng(2000, ol.rng_seed(777), trace=False)
+    assert st["nsuc"][776] == o.stats()["nsuc"]
+
+
+def test_fp64_peak_microbenchmark_is_sane():
+    from montecarlo_b200.engine import measure_fp64_peak
+    tf = measure_fp64_peak(0, 50.0)
+    assert 10.0 < tf < 60.0, tf

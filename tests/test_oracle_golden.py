@@ -140,29 +140,24 @@ def test_replay_reference_trace(shipped, name):
     assert abs(ch.stats()["toteng_old"] - float(t["final_energy"])) <= 2 * PRINT11 * abs(float(t["final_energy"]))
 
 
-def test_rng_stream_is_documented_xoshiro():
-    """u = (xoshiro256**(splitmix64(seed)) >> 11) * 2^-53; first outputs for seed 1 written out in python."""
+def test_rng_stream_is_documented():
+    """key = mix(seed + G); u_n = (mix(key + (n+1) G) >> 11) * 2^-53 — restated here in python integers."""
     M = (1 << 64) - 1
+    G = 0x9E3779B97F4A7C15
 
-    def splitmix(z):
-        z = (z + 0x9E3779B97F4A7C15) & M
-        x = z
+    def mix(x):
         x = ((x ^ (x >> 30)) * 0xBF58476D1CE4E5B9) & M
         x = ((x ^ (x >> 27)) * 0x94D049BB133111EB) & M
-        return z, x ^ (x >> 31)
+        return x ^ (x >> 31)
 
-    def rotl(x, k):
-        return ((x << k) | (x >> (64 - k))) & M
-
-    z, s = 1, []
-    for _ in range(4):
-        z, v = splitmix(z)
-        s.append(v)
-    st = ol.rng_seed(1)
-    assert [int(v) for v in st] == s
-    got = ol.rng_uniforms(st, 5)
-    for g in got:
-        r = (rotl((s[1] * 5) & M, 7) * 9) & M
-        t = (s[1] << 17) & M
-        s[2] ^= s[0]; s[3] ^= s[1]; s[1] ^= s[2]; s[0] ^= s[3]; s[2] ^= t; s[3] = rotl(s[3], 45)
-        assert g == (r >> 11) * 2.0 ** -53 and 0.0 <= g < 1.0
+    for seed in (0, 1, 2, 1024, M):
+        st = ol.rng_seed(seed)
+        key = mix((seed + G) & M)
+        assert int(st[0]) == key and int(st[1]) == 0
+        got = ol.rng_uniforms(st, 9)
+        for n, g in enumerate(got):
+            assert g == (mix((key + (n + 1) * G) & M) >> 11) * 2.0 ** -53 and 0.0 <= g < 1.0
+        assert int(st[1]) == 9
+    a = ol.rng_uniforms(ol.rng_seed(1), 4096)
+    b = ol.rng_uniforms(ol.rng_seed(2), 4096)
+    assert abs(a.mean() - 0.5) < 0.02 and abs(np.corrcoef(a, b)[0, 1]) < 0.06
