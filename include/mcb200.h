@@ -38,7 +38,8 @@ typedef struct {
     int device;             /* CUDA ordinal; -1 = the current device */
     int quirk_31;           /* 1 = keep `IF (RSOLV .EQ. 31) RSOLV = 30` (MonteCarlo.F90:698) in mcb_run_steps */
     int matrix_mode;        /* 0 auto, 1 force the pair matrix into global memory (never shared memory) */
-    int reserved;
+    int lookahead;          /* steps of a chain evaluated speculatively at once by mcb_run_steps' built-in-stream
+                               path: 1, 2 or 4; 0 = default (2).  Does not change any decision of the chain. */
     double boxl;            /* half side, Angstrom */
     double cutoff;          /* centre-of-mass cutoff, 7.0 in the reference (MonteCarlo.F90:812) */
     double conv;            /* factor on the Coulomb sum; the reference's value is exactly 0.0 (LennardJones.f90:57) */
@@ -120,15 +121,20 @@ int mcb_commit(mcb_t *h, int nchains, const unsigned char *accept);
 
 /* ---- batched mode: MCINIT + calculateLJ + calcEnergy + METROPOLIS looped on the GPU ----------------- */
 int mcb_set_mc_params(mcb_t *h, int chain0, int nchains, const mcb_mc_params *p, int broadcast);
-/* Uniform stream used when mcb_run_steps gets no buffer:  key = mix(seed + G), u_n = (mix(key + (n+1)*G) >> 11) * 2^-53,
- * G = 0x9E3779B97F4A7C15, mix = splitmix64's finaliser; n counts the uniforms the chain has consumed.
- * (The reference's own RNG is the compiler's RANDOM_NUMBER seeded from /dev/urandom, MC_lib/randgen.f90:15-40,
- * so there is no reference stream to reproduce; a driver that wants its own stream passes a buffer.) */
+/* Uniform stream used when mcb_run_steps gets no buffer: counter-based and random-access,
+ *   G = 0x9E3779B97F4A7C15, mix = splitmix64's finaliser, key = mix(seed + G),
+ *   u(n) = (mix(key + (n+1)*G) >> 11) * 2^-53 in [0,1);
+ * Metropolis step s (0-based, counted over the chain's life: mcb_chain_stats.step) reads u(8s) .. u(8s+6) for
+ * MCINIT and u(8s+7) if METROPOLIS draws.  (The reference's own RNG is the compiler's RANDOM_NUMBER seeded from
+ * /dev/urandom, MC_lib/randgen.f90:15-40: there is no reference stream to reproduce; a driver that wants its
+ * own stream passes a buffer.) */
 int mcb_seed_chains(mcb_t *h, int chain0, int nchains, const uint64_t *seeds);
 /* replaces: loop_LJ (MonteCarlo.F90:406-433) for nsteps steps of every chain.  uniforms: NULL (built-in
  * stream) or host [n_chains][cap] doubles in [0,1): each step consumes 7 (MCINIT :697-700, lib.f90:115-130)
  * plus 1 only when METROPOLIS draws (:739).  A chain stops early when fewer than 8 remain; consumed[c]
- * (may be NULL) receives how many it used, steps_done[c] (may be NULL) how many steps it made. */
+ * (may be NULL) receives how many it used, steps_done[c] (may be NULL) how many steps it made.  With
+ * uniforms, consumed and steps_done all NULL the call only enqueues the kernel on the handle's stream and
+ * returns; any later call that reads results (mcb_get_stats, mcb_get_chain_state, ...) waits for it. */
 int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, int64_t cap, int64_t *consumed,
                   int64_t *steps_done);
 int mcb_get_stats(mcb_t *h, int chain0, int nchains, mcb_chain_stats *out);

@@ -6,12 +6,13 @@ fails loudly: there is no Python or CPU fallback for anything it computes.
 from __future__ import annotations
 
 import ctypes as C
+import os
 import subprocess
 from pathlib import Path
 
 PKG = Path(__file__).resolve().parent
 ROOT = PKG.parent
-LIB_PATH = PKG / "libmcb200.so"
+LIB_PATH = Path(os.environ.get("MCB200_LIB", PKG / "libmcb200.so"))  # override: debug builds only
 SOURCES = [PKG / "csrc" / "mcb200.cu"]
 HEADERS = [PKG / "csrc" / "mcb_device.cuh", PKG / "csrc" / "mcb_kernels.cuh", ROOT / "include" / "mcb200.h"]
 
@@ -27,7 +28,7 @@ _u8p = C.POINTER(C.c_ubyte)
 
 class McbParams(C.Structure):
     _fields_ = [("n_mol", C.c_int), ("n_sites", C.c_int), ("n_sol", C.c_int), ("n_chains", C.c_int),
-                ("device", C.c_int), ("quirk_31", C.c_int), ("matrix_mode", C.c_int), ("reserved", C.c_int),
+                ("device", C.c_int), ("quirk_31", C.c_int), ("matrix_mode", C.c_int), ("lookahead", C.c_int),
                 ("boxl", C.c_double), ("cutoff", C.c_double), ("conv", C.c_double),
                 ("site_rel", _dp), ("site_tab", _dp)]
 

@@ -32,7 +32,8 @@ struct mcb_handle {
     std::vector<double> site_tab;                     // [4][3] padded
     std::vector<double> tab0AB, tab0Q;                // type-0 tables
     long long launches = 0;
-    size_t smem_bytes = 0;
+    size_t smem_bytes = 0, smem_spec_bytes = 0;
+    int lookahead = 4;
     std::string err;
 };
 
@@ -82,18 +83,24 @@ static void setup_geo(mcb_handle *h)
     g.o_tabQ = g.o_tabAB + (1 + g.nsolp) * 32;
     int end_tab = g.o_tabQ + (1 + g.nsolp) * 16;
     g.o_mat = end_tab;
-    g.o_newrow = 0; g.o_list = g.Np; g.o_pend = g.Np + g.Np / 2;
-    g.work_doubles = (int)round_up(g.o_pend + (sizeof(Pending) + 7) / 8, 2);
+    g.o_newrow = 0; g.o_list = g.Np;
+    g.o_epart = (int)round_up(g.o_list + (g.Np + g.nsolp + 1) / 2, 2);
+    g.o_pend = g.o_epart + 4 * (g.Np + g.nsolp);
+    g.o_touch = (int)round_up(g.o_pend + (sizeof(Pending) + 7) / 8, 2);
+    g.work_doubles = (int)round_up(g.o_touch + ((g.N + 31) / 32 + 1) / 2, 2);
+    g.spec_group_doubles = g.work_doubles;
     size_t with_mat = round_up((size_t)end_tab + (size_t)g.N * g.MS, 2);
     // the matrix rides in shared memory while a chain's footprint leaves room for >= 7 chains per SM
-    bool mat_smem = p.matrix_mode != 1 && (with_mat + g.work_doubles) * 8 <= 32 * 1024;
+    bool mat_smem = p.matrix_mode != 1 && (with_mat + 4 * (size_t)g.work_doubles) * 8 <= 32 * 1024;
     g.mat_in_image = mat_smem ? 1 : 0;
     g.image_doubles = (int)(mat_smem ? with_mat : (size_t)end_tab);
     g.stage_doubles = g.image_doubles;
     g.quirk31 = p.quirk_31;
     g.boxl = p.boxl; g.boxl2 = p.boxl * 2.0; g.inv_boxl = 1.0 / p.boxl; g.cut2 = exact_cut2(p.cutoff); g.conv = p.conv;
+    h->lookahead = p.lookahead == 1 || p.lookahead == 2 || p.lookahead == 4 ? p.lookahead : 2;
     h->smem_bytes = ((size_t)g.stage_doubles + g.work_doubles) * 8;
-    h->can_step = h->smem_bytes <= 227 * 1024;
+    h->smem_spec_bytes = ((size_t)g.stage_doubles + (size_t)h->lookahead * g.work_doubles) * 8;
+    h->can_step = h->smem_spec_bytes <= 227 * 1024;
 }
 
 extern "C" const char *mcb_last_error(const mcb_t *h) { return h ? h->err.c_str() : g_create_err.c_str(); }
@@ -111,10 +118,10 @@ extern "C" int mcb_destroy(mcb_t *h)
 }
 
 template <typename K>
-static int set_smem_attr(mcb_handle *h, K kernel)
+static int set_smem_attr(mcb_handle *h, K kernel, size_t bytes)
 {
-    if (h->smem_bytes > 48 * 1024)
-        CK(h, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_bytes));
+    if (bytes > 48 * 1024)
+        CK(h, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     return 0;
 }
 
@@ -191,10 +198,12 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
     CKC(cudaMemcpy(h->ctl, ctl.data(), nc * sizeof(ChainCtl), cudaMemcpyHostToDevice));
     if (h->can_step) {
         int rc = 0;
-        rc |= set_smem_attr(h, k_run_steps<false, false, false>); rc |= set_smem_attr(h, k_run_steps<false, false, true>);
-        rc |= set_smem_attr(h, k_run_steps<false, true, false>);  rc |= set_smem_attr(h, k_run_steps<false, true, true>);
-        rc |= set_smem_attr(h, k_run_steps<true, false, false>);  rc |= set_smem_attr(h, k_run_steps<true, false, true>);
-        rc |= set_smem_attr(h, k_run_steps<true, true, false>);   rc |= set_smem_attr(h, k_run_steps<true, true, true>);
+        rc |= set_smem_attr(h, k_run_steps<false, true, false>, h->smem_bytes); rc |= set_smem_attr(h, k_run_steps<false, true, true>, h->smem_bytes);
+        rc |= set_smem_attr(h, k_run_steps<true, true, false>, h->smem_bytes);  rc |= set_smem_attr(h, k_run_steps<true, true, true>, h->smem_bytes);
+#define SPEC_ATTR(GL) rc |= set_smem_attr(h, k_run_spec<false, false, GL>, h->smem_spec_bytes); rc |= set_smem_attr(h, k_run_spec<false, true, GL>, h->smem_spec_bytes); \
+                      rc |= set_smem_attr(h, k_run_spec<true, false, GL>, h->smem_spec_bytes);  rc |= set_smem_attr(h, k_run_spec<true, true, GL>, h->smem_spec_bytes);
+        SPEC_ATTR(8) SPEC_ATTR(16) SPEC_ATTR(32)
+#undef SPEC_ATTR
         if (rc) return fail(rc);
     }
 #undef CKC
@@ -487,13 +496,30 @@ extern "C" int mcb_get_stats(mcb_t *h, int chain0, int nchains, mcb_chain_stats 
     return 0;
 }
 
-template <bool COUL, bool UBUF>
-static void launch_run(mcb_t *h, long long nsteps, long long cap, long long *d_consumed, long long *d_steps)
+template <bool COUL>
+static void launch_run_ubuf(mcb_t *h, long long nsteps, long long cap, long long *d_consumed, long long *d_steps)
 {
     if (h->g.mat_in_image)
-        k_run_steps<COUL, UBUF, true><<<h->n_chains, 32, h->smem_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, h->d_ubuf, cap, d_consumed, d_steps);
+        k_run_steps<COUL, true, true><<<h->n_chains, 32, h->smem_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, h->d_ubuf, cap, d_consumed, d_steps);
     else
-        k_run_steps<COUL, UBUF, false><<<h->n_chains, 32, h->smem_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, h->d_ubuf, cap, d_consumed, d_steps);
+        k_run_steps<COUL, true, false><<<h->n_chains, 32, h->smem_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, h->d_ubuf, cap, d_consumed, d_steps);
+}
+
+template <bool COUL, int GL>
+static void launch_run_spec(mcb_t *h, long long nsteps, long long *d_steps)
+{
+    if (h->g.mat_in_image)
+        k_run_spec<COUL, true, GL><<<h->n_chains, 32, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps);
+    else
+        k_run_spec<COUL, false, GL><<<h->n_chains, 32, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps);
+}
+
+template <bool COUL>
+static void launch_run_spec_any(mcb_t *h, long long nsteps, long long *d_steps)
+{
+    if (h->lookahead == 4) launch_run_spec<COUL, 8>(h, nsteps, d_steps);
+    else if (h->lookahead == 2) launch_run_spec<COUL, 16>(h, nsteps, d_steps);
+    else launch_run_spec<COUL, 32>(h, nsteps, d_steps);
 }
 
 extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, int64_t cap, int64_t *consumed, int64_t *steps_done)
@@ -515,10 +541,17 @@ extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, i
         CK(h, cudaMemcpyAsync(h->d_ubuf, uniforms, need * sizeof(double), cudaMemcpyHostToDevice, h->stream));
     }
     long long *d_consumed = h->d_ll, *d_steps = h->d_ll + nc;
-    if (uniforms) { if (h->coul) launch_run<true, true>(h, nsteps, cap, d_consumed, d_steps); else launch_run<false, true>(h, nsteps, cap, d_consumed, d_steps); }
-    else { if (h->coul) launch_run<true, false>(h, nsteps, 0, d_consumed, d_steps); else launch_run<false, false>(h, nsteps, 0, d_consumed, d_steps); }
+    if (nsteps > (1LL << 30)) return arg_err(h, "mcb_run_steps: at most 2^30 steps per call");
+    if (uniforms) { if (h->coul) launch_run_ubuf<true>(h, nsteps, cap, d_consumed, d_steps); else launch_run_ubuf<false>(h, nsteps, cap, d_consumed, d_steps); }
+    else {
+        CK(h, cudaMemsetAsync(d_consumed, 0, sizeof(long long) * nc, h->stream));
+        if (h->coul) launch_run_spec_any<true>(h, nsteps, d_steps); else launch_run_spec_any<false>(h, nsteps, d_steps);
+    }
     h->launches++;
     CK(h, cudaGetLastError());
+    // nothing to hand back: the launch stays asynchronous on the handle's stream (the next call that reads
+    // results, e.g. mcb_get_stats, synchronises)
+    if (!uniforms && !consumed && !steps_done) return 0;
     std::vector<long long> tmp;
     if (consumed || steps_done) {
         tmp.resize(2 * nc);
@@ -565,3 +598,12 @@ extern "C" int mcb_measure_fp64_peak(int device, double ms, double *tflops)
     *tflops = best;
     return 0;
 }
+
+#ifdef MCB_PHASE_CLOCKS
+extern "C" int mcb_debug_phase_clocks(unsigned long long *out, int reset)
+{
+    if (out && cudaMemcpyFromSymbol(out, g_phase, sizeof(unsigned long long) * 8) != cudaSuccess) return -1;
+    if (reset) { unsigned long long z[8] = {0}; if (cudaMemcpyToSymbol(g_phase, z, sizeof(z)) != cudaSuccess) return -1; }
+    return 0;
+}
+#endif

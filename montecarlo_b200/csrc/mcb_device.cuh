@@ -34,8 +34,9 @@ struct Geo {
     int o_com, o_hoek, o_energy, o_sites, o_tabAB, o_tabQ, o_mat;
     int image_doubles;      // per-chain stride of the image array in HBM (includes mat iff mat_in_image)
     int stage_doubles;      // how much of the image is copied to shared memory
-    int o_newrow, o_list, o_pend;  // work arrays (shared memory in k_run_steps, scratch in the single-step kernels)
-    int work_doubles;       // size of the work area (newrow + list), in doubles
+    int o_newrow, o_list, o_epart, o_pend, o_touch;  // work arrays (shared memory in k_run_steps, scratch in the single-step kernels)
+    int work_doubles;       // size of one work area, in doubles
+    int spec_group_doubles; // stride between the work areas of the look-ahead groups of k_run_spec (= work_doubles)
     int mat_in_image;
     int quirk31;
     double boxl, boxl2, inv_boxl, cut2, conv;
@@ -56,7 +57,7 @@ struct ChainPtrs {
     const double *tabAB, *tabQ;
     double *mat;     // row stride g.MS
     double *newrow;  // [Np]
-    int *list;       // [Np]
+    int *list;       // [nsolp + Np]
 };
 
 __device__ __forceinline__ ChainPtrs chain_ptrs(const Geo &g, double *img, double *mat, double *work)
@@ -77,49 +78,57 @@ __device__ __forceinline__ double warp_sum(double v)
     return v;
 }
 
-// Minimum image exactly as the reference writes it: R - BOXL2*AINT(R/BOXL), BOXL = half side
-// (LennardJones.f90:178-180).  Not a nearest image once |R| >= 2*BOXL; that is part of the contract.
-// The quotient is formed with the reciprocal: it can differ from R/BOXL only within one ulp of an integer.
-__device__ __forceinline__ double mic_fast(double d, const Geo &g) { return fma(-g.boxl2, trunc(d * g.inv_boxl), d); }
-// With the true division, for the centre-of-mass gate and the wraps (MonteCarlo.F90:705-712, :808-810).
+// Minimum image as the reference writes it, R - BOXL2*AINT(R/BOXL) with BOXL = half side
+// (LennardJones.f90:178-180) — not a nearest image once |R| >= 2*BOXL, and that is part of the contract.
+// Only the SQUARE of the result is ever used, so the kernel works on |R|:
+//     |R - BOXL2*AINT(R/BOXL)| = | |R| - BOXL2*floor(|R|/BOXL) |
+// and floor comes from one round-down FMA onto 2^52 (whose ulp is 1) instead of an fp64 FRND, which on B200
+// issues once per ~13 cycles per warp (tools/latency.cu) and would cost as much as all the DFMAs of a site pair.
+// The quotient uses the reciprocal of BOXL: it can pick the other image only when |R|/BOXL is within an ulp
+// of an integer, where both images are equally far (to 1e-15), so r^2 and the energy do not notice.
+__device__ __forceinline__ double mic_abs(double d, const Geo &g)
+{
+    const double a = fabs(d);
+    const double t = __fma_rd(a, g.inv_boxl, 4503599627370496.0) - 4503599627370496.0;
+    return fma(-g.boxl2, t, a);
+}
+// With the true division, for the coordinate wraps of MCINIT (MonteCarlo.F90:705-712).
 __device__ __forceinline__ double wrap_exact(double x, double period, double half) { return x - period * trunc(x / half); }
 
-#ifndef MCB_RCP_NEWTON
-#define MCB_RCP_NEWTON 2  // seed is good to ~2^-20; two steps reach fp64 (checked on the GPU in tests/test_gpu_parity.py)
-#endif
-// 1/x for x in the range of squared site distances: MUFU.RCP64H seed + two Newton steps (no denormal /
-// overflow fix-up path: r^2 = 0 gives NaN, which METROPOLIS clamps and rejects like the reference's Inf-Inf).
+// 1/x for squared site distances: MUFU.RCP64H seed (~2^-20) and one cubically convergent step
+// y = y0*(1 + e + e^2), e = 1 - x*y0 (no denormal/overflow fix-up: r^2 = 0 gives NaN, which METROPOLIS clamps
+// and rejects like the reference's Inf - Inf).
 __device__ __forceinline__ double rcp_nr(double x)
 {
     double y;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
-    double e = fma(-x, y, 1.0);
-    y = fma(y, e, y);
-    e = fma(-x, y, 1.0);
-    y = fma(y, e, y);
-#if MCB_RCP_NEWTON > 2
-    e = fma(-x, y, 1.0);
-    y = fma(y, e, y);
-#endif
-    return y;
+    const double e = fma(-x, y, 1.0);
+    return fma(y, fma(e, e, e), y);
 }
 
-// One site pair, LJ_FORMULA (LennardJones.f90:153-187) with tabulated A = 4 eps s^12, B = 4 eps s^6:
-// 4 eps (s^12/r^12 - s^6/r^6) = s6*(A*s6 - B), s6 = (1/r^2)^3.
-template <bool COUL>
-__device__ __forceinline__ double site_pair(double dx, double dy, double dz, double A, double B, double QQ, const Geo &g)
+// Squared minimum-image distance of one site pair (LJ_FORMULA, LennardJones.f90:178-182).
+__device__ __forceinline__ double pair_r2(double dx, double dy, double dz, const Geo &g)
 {
-    dx = mic_fast(dx, g); dy = mic_fast(dy, g); dz = mic_fast(dz, g);
-    double r2 = fma(dz, dz, fma(dy, dy, dx * dx));
+    dx = mic_abs(dx, g); dy = mic_abs(dy, g); dz = mic_abs(dz, g);
+    return fma(dz, dz, fma(dy, dy, dx * dx));
+}
+
+// acc + one site pair's energy.  LJ_FORMULA (LennardJones.f90:153-187) with tabulated A = 4 eps s^12,
+// B = 4 eps s^6:  4 eps (s^12/r^12 - s^6/r^6) = s6*(A*s6 - B), s6 = (1/r^2)^3;  Coulomb q1 q2 conv / r.
+template <bool COUL>
+__device__ __forceinline__ double site_pair_acc(double acc, double dx, double dy, double dz, double A, double B, double QQ,
+                                                const Geo &g)
+{
+    const double r2 = pair_r2(dx, dy, dz, g);
     if (COUL) {
-        double rinv = rsqrt(r2);          // q1 q2 / r * conv  (LennardJones.f90:184, :80)
-        double inv = rinv * rinv;
-        double s6 = inv * inv * inv;
-        return fma(s6, fma(A, s6, -B), QQ * rinv);
+        const double rinv = rsqrt(r2);
+        const double inv = rinv * rinv;
+        const double s6 = inv * inv * inv;
+        return fma(s6, fma(A, s6, -B), fma(QQ, rinv, acc));
     } else {
-        double inv = rcp_nr(r2);
-        double s6 = inv * inv * inv;
-        return s6 * fma(A, s6, -B);
+        const double inv = rcp_nr(r2);
+        const double s6 = inv * inv * inv;
+        return fma(s6, fma(A, s6, -B), acc);
     }
 }
 
@@ -136,7 +145,8 @@ __device__ __forceinline__ void rotate_site(double c1, double s1, double c2, dou
     oz = cz + (m31 * rx + m32 * ry + m33 * rz);
 }
 
-// Uniform stream (include/mcb200.h, mcb_seed_chains): u_n = (mix(key + (n+1) G) >> 11) * 2^-53.
+// Uniform stream (include/mcb200.h, mcb_seed_chains): u_n = (mix(key + (n+1) G) >> 11) * 2^-53, random access
+// in n; Metropolis step s (0-based) of a chain owns n = 8 s .. 8 s + 7.
 __device__ __forceinline__ unsigned long long mix64(unsigned long long x)
 {
     x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
@@ -168,10 +178,7 @@ __device__ __forceinline__ int row_eval(const Geo &g, const ChainPtrs &p, int i,
         int j = j0 + lane;
         bool in = false;
         if (j < jlimit && j != i) {
-            double dx = wrap_exact(p.com[j] - ncx, g.boxl2, g.boxl);              // R = CoM(J) - CoM(I), :806-810
-            double dy = wrap_exact(p.com[g.Np + j] - ncy, g.boxl2, g.boxl);
-            double dz = wrap_exact(p.com[2 * g.Np + j] - ncz, g.boxl2, g.boxl);
-            double r2 = dx * dx + dy * dy + dz * dz;                              // length_sq, vector_class.f90:107
+            double r2 = pair_r2(p.com[j] - ncx, p.com[g.Np + j] - ncy, p.com[2 * g.Np + j] - ncz, g);   // R = CoM(J) - CoM(I), :806-810
             in = !(r2 > g.cut2);   // cut2 = largest x with sqrt(x) <= cutoff: same decision as length(R) .GT. 7.D0
         }
         unsigned m = __ballot_sync(FULL, in);
@@ -197,11 +204,10 @@ __device__ __forceinline__ int row_eval(const Geo &g, const ChainPtrs &p, int i,
             double q0 = 0, q1 = 0, q2 = 0, q3 = 0;
             if (COUL) { const double *tq = p.tabQ + (t * 4 + a) * 4; q0 = tq[0]; q1 = tq[1]; q2 = tq[2]; q3 = tq[3]; }
             // R = mol2(J) - mol1(I) (LennardJones.f90:69); b = 0..3 inner like the reference's J loop
-            double e0 = site_pair<COUL>(v0.x - sx, v0.y - sy, v1.x - sz, p0.x, p0.y, q0, g);
-            double e1 = site_pair<COUL>(v1.y - sx, v2.x - sy, v2.y - sz, p1.x, p1.y, q1, g);
-            double e2 = site_pair<COUL>(v3.x - sx, v3.y - sy, v4.x - sz, p2.x, p2.y, q2, g);
-            double e3 = site_pair<COUL>(v4.y - sx, v5.x - sy, v5.y - sz, p3.x, p3.y, q3, g);
-            e = ((e0 + e1) + e2) + e3;
+            e = site_pair_acc<COUL>(0.0, v0.x - sx, v0.y - sy, v1.x - sz, p0.x, p0.y, q0, g);
+            e = site_pair_acc<COUL>(e, v1.y - sx, v2.x - sy, v2.y - sz, p1.x, p1.y, q1, g);
+            e = site_pair_acc<COUL>(e, v3.x - sx, v3.y - sy, v4.x - sz, p2.x, p2.y, q2, g);
+            e = site_pair_acc<COUL>(e, v4.y - sx, v5.x - sy, v5.y - sz, p3.x, p3.y, q3, g);
         }
         e += shfl_xor_d(e, 1);
         e += shfl_xor_d(e, 2);

@@ -148,10 +148,53 @@ __global__ void __launch_bounds__(32) k_commit(Geo g, double *images, double *ma
     if (lane == 0) pd->valid = 0;
 }
 
+#ifdef MCB_PHASE_CLOCKS
+// Debug build only (-DMCB_PHASE_CLOCKS): cycles per phase of k_run_steps, summed over warps.
+__device__ unsigned long long g_phase[8];
+#define PH_T(k) do { long long now_ = clock64(); ph[k] += now_ - tph; tph = now_; } while (0)
+#else
+#define PH_T(k) do { } while (0)
+#endif
+
+// x - period*AINT(x/half) with the quotient formed by a multiplication; when the product lands within 1e-13
+// of an integer (where the rounding of x/half could matter) the true division decides, so the result is
+// always the one the reference's expression gives (MonteCarlo.F90:705-712, :808-810).
+__device__ __forceinline__ double wrap_checked(double x, double period, double half, double inv_half)
+{
+    double q = x * inv_half;
+    double t = trunc(q);
+    double f = fabs(q - t);
+    if (f < 1e-13 || f > 1.0 - 1e-13) t = trunc(x / half);
+    return fma(-period, t, x);
+}
+
+// One (partner, own site a) item: own site (sx,sy,sz) against the four sites of virtual molecule vm with the
+// (A,B[,QQ]) row of type t.  R = mol2(J) - mol1(I) (LennardJones.f90:69), b inner like the reference's J loop.
+template <bool COUL>
+__device__ __forceinline__ double item_energy(const Geo &g, const double *sites, const double *tabAB, const double *tabQ,
+                                              int vm, int t, int a, double sx, double sy, double sz)
+{
+    const double2 *sp = reinterpret_cast<const double2 *>(sites + SITE_DOUBLES * vm);
+    const double2 *ab = reinterpret_cast<const double2 *>(tabAB) + (t * 4 + a) * 4;
+    double2 v0 = sp[0], v1 = sp[1], v2 = sp[2], v3 = sp[3], v4 = sp[4], v5 = sp[5];
+    double2 p0 = ab[0], p1 = ab[1], p2 = ab[2], p3 = ab[3];
+    double q0 = 0, q1 = 0, q2 = 0, q3 = 0;
+    if (COUL) { const double *tq = tabQ + (t * 4 + a) * 4; q0 = tq[0]; q1 = tq[1]; q2 = tq[2]; q3 = tq[3]; }
+    double ea = site_pair_acc<COUL>(0.0, v0.x - sx, v0.y - sy, v1.x - sz, p0.x, p0.y, q0, g);
+    double eb = site_pair_acc<COUL>(0.0, v1.y - sx, v2.x - sy, v2.y - sz, p1.x, p1.y, q1, g);
+    ea = site_pair_acc<COUL>(ea, v3.x - sx, v3.y - sy, v4.x - sz, p2.x, p2.y, q2, g);
+    eb = site_pair_acc<COUL>(eb, v4.y - sx, v5.x - sy, v5.y - sz, p3.x, p3.y, q3, g);
+    return ea + eb;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Batched mode: nsteps Metropolis steps of one chain per warp, the chain's image resident in shared memory.
 //   UBUF      uniforms come from a caller buffer [chain][cap] instead of the built-in counter stream
 //   MAT_SMEM  the pair matrix is part of the staged image (small N); otherwise it stays in global memory
+// A chain's steps are strictly sequential and one step is only ~230 site pairs, so the kernel is shaped for
+// LATENCY: the old row is fetched as soon as the molecule is known; 16 partner slots (two per lane, eight
+// independent site pairs) are in flight at once; dE comes from a single warp reduction of per-lane partial
+// sums; the per-partner energies are parked in shared memory and only summed if the move is accepted.
 template <bool COUL, bool UBUF, bool MAT_SMEM>
 __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl,
                                                   long long nsteps, const double *ubuf, long long cap,
@@ -160,7 +203,7 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
     extern __shared__ __align__(16) double smem[];
     const int lane = threadIdx.x;
     const int c = blockIdx.x;
-    const int N = g.N, Np = g.Np, MS = g.MS;
+    const int N = g.N, Np = g.Np, MS = g.MS, nsolp = g.nsolp;
     double *gimg = images + (size_t)c * g.image_doubles;
     double *img = smem;
     {   // stage the image: linear, coalesced 16-byte loads
@@ -169,8 +212,14 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
         for (int k = lane; k < g.stage_doubles / 2; k += 32) dst[k] = src[k];
     }
     double *mat = MAT_SMEM ? img + g.o_mat : matg + (size_t)c * N * MS;
-    ChainPtrs p = chain_ptrs(g, img, mat, smem + g.stage_doubles);
+    double *const com = img + g.o_com, *const hoek = img + g.o_hoek, *const energy = img + g.o_energy;
+    double *const sites = img + g.o_sites;
+    const double *const tabAB = img + g.o_tabAB, *const tabQ = img + g.o_tabQ;
+    double *const wk = smem + g.stage_doubles;
+    int *const list = reinterpret_cast<int *>(wk + g.o_list);      // [nsolp + N]: virtual molecule of each slot
+    double *const epart = wk + g.o_epart;                          // [nsolp + N][4]: per (slot, own site) energy
     ChainCtl s = ctl[c];
+    for (int p = lane; p < nsolp; p += 32) list[p] = N + p;        // the solute pseudo-molecules are slots 0..nsolp-1
     __syncwarp();
 
     // re-anchor TOTENG on the stored matrix so that rounding of the running sum cannot accumulate across launches
@@ -178,30 +227,41 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
         double acc = 0.0;
         for (int i = 0; i < N; ++i)
             for (int j = i + 1 + lane; j < N; j += 32) acc += mat[(size_t)i * MS + j];
-        for (int i = lane; i < N; i += 32) acc += p.energy[i];
+        for (int i = lane; i < N; i += 32) acc += energy[i];
         s.toteng = warp_sum(acc);
     }
 
-    const int a = lane & 3;
+    const int a = lane & 3, q = lane >> 2;
+    const unsigned lt = (1u << lane) - 1u;
     const double relx = rel.r[3 * a], rely = rel.r[3 * a + 1], relz = rel.r[3 * a + 2];
     const int wpair = rel.n_sites * rel.n_sites, wsol = rel.n_sites * g.nsol;
-    const double rt = 8.314 * s.temperature;                       // MonteCarlo.F90:729
+    const double neg_inv_rt = -1000.0 / (8.314 * s.temperature);   // EXPONENT = -DELTA*1000/(8.314*T), MonteCarlo.F90:729
     const int r = min(max(lane - 1, 0), 5);
     const bool isang = r >= 3;
     const int k = isang ? r - 3 : r;
-    double *const base = (isang ? p.hoek : p.com) + k * Np;
+    double *const base = (isang ? hoek : com) + k * Np;
     const double period = isang ? TAU_D : g.boxl2, half = isang ? PI_D : g.boxl;
+    const double inv_half = isang ? 1.0 / PI_D : g.inv_boxl;
+    const double f1 = isang ? 1.0 : INV_SQRT3;
     int adj_count = (int)(s.step % s.nadj);
-    long long cursor = 0, done = 0;
+    long long cursor = 0;
+    int done = 0;
+    unsigned nsuc = 0, nacc = (unsigned)s.naccept, racc = 0, nclamp = 0, uused = 0, prod_acc = 0, nstat = 0;
+    unsigned long long sitepairs = 0;
+    const unsigned long long step0 = (unsigned long long)s.step;
     const double *myubuf = UBUF ? ubuf + (size_t)c * cap : nullptr;
+    const int nsteps_i = (int)min(nsteps, (long long)0x7fffffff);
+#ifdef MCB_PHASE_CLOCKS
+    long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tph = clock64();
+#endif
 
-    for (; done < nsteps; ++done) {
+    for (; done < nsteps_i; ++done) {
         double myu;
         if (UBUF) {
             if (cursor + 8 > cap) break;
             myu = lane < 8 ? myubuf[cursor + lane] : 0.0;
         } else {
-            myu = stream_uniform(s.rng_key, s.rng_n + (unsigned long long)(lane & 7));
+            myu = stream_uniform(s.rng_key, 8ULL * (step0 + (unsigned)done) + (unsigned)(lane & 7));
         }
         // ---- MCINIT (MonteCarlo.F90:685-715): lane 0 picks the molecule, lanes 1-3 move the centre of mass,
         //      lanes 4-6 the angles (randVec / randVecHoek, lib.f90:111-131), then the wraps (:705-712)
@@ -209,10 +269,13 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
         int i = (int)(u0 * (double)N) + 1;
         if (g.quirk31 && i == 31) i = 30;                         // :698
         i = min(i, N) - 1;
+        // old row of the pair matrix + ENERGY(i): needed only for dE, fetched now to hide the latency
+        double old_part = lane == 0 ? energy[i] : 0.0;
+        for (int j = lane; j < N; j += 32) old_part += mat[(size_t)i * MS + j];
         double rv = (myu - 0.5) * 2.0;
-        rv = (isang ? 1.0 : INV_SQRT3) * rv;
+        rv = f1 * rv;
         rv = (isang ? s.dhoekmax : s.dposmax) * rv;
-        double nv = wrap_exact(base[i] + rv, period, half);
+        const double nv = wrap_checked(base[i] + rv, period, half, inv_half);
         double sn, cs;
         sincos(nv, &sn, &cs);
         const double ncx = shfl_d(nv, 1), ncy = shfl_d(nv, 2), ncz = shfl_d(nv, 3);
@@ -220,64 +283,379 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
                      c3 = shfl_d(cs, 6), s3 = shfl_d(sn, 6);
         double sx, sy, sz;
         rotate_site(c1, s1, c2, s2, c3, s3, relx, rely, relz, ncx, ncy, ncz, sx, sy, sz);
+        PH_T(0);
 
-        // ---- calculateLJ(RSOLV) (:792-828) as a difference against the stored row, then calcEnergy (:988-1004)
-        double e_sol;
-        const int nn = row_eval<COUL>(g, p, i, N, ncx, ncy, ncz, sx, sy, sz, lane, e_sol);
-        double d = 0.0;
-        for (int j = lane; j < N; j += 32) d += p.newrow[j] - mat[(size_t)i * MS + j];
-        const double dE = warp_sum(d) + (e_sol - p.energy[i]);
+        // ---- calculateLJ(RSOLV) (:792-828): centre-of-mass gate, one partner per lane (:804-813)
+        int nn = 0;
+        for (int j0 = 0; j0 < N; j0 += 32) {
+            const int j = j0 + lane;
+            bool in = false;
+            if (j < N && j != i) {
+                in = !(pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2);
+            }
+            const unsigned m = __ballot_sync(FULL, in);
+            if (in) list[nsolp + nn + __popc(m & lt)] = j;
+            nn += __popc(m);
+        }
+        __syncwarp();
+        PH_T(1);
+        // ---- site pairs: 16 slots per pass, two (slot, own site) items per lane (calcLJ / CalcLJ_SV)
+        const int nslots = nsolp + nn;
+        double lane_tot = 0.0;
+        for (int s0 = 0; s0 < nslots; s0 += 16) {
+            const int sA = s0 + q, sB = s0 + 8 + q;
+            double eA = 0.0, eB = 0.0;
+            if (sA < nslots) eA = item_energy<COUL>(g, sites, tabAB, tabQ, list[sA], sA < nsolp ? 1 + sA : 0, a, sx, sy, sz);
+            if (sB < nslots) eB = item_energy<COUL>(g, sites, tabAB, tabQ, list[sB], sB < nsolp ? 1 + sB : 0, a, sx, sy, sz);
+            if (sA < nslots) epart[4 * sA + a] = eA;
+            if (sB < nslots) epart[4 * sB + a] = eB;
+            lane_tot += eA + eB;
+        }
+        PH_T(2);
+        // ---- calcEnergy as a difference (:988-1004): TOTENG_new - TOTENG_old = sum(new row) - sum(old row)
+        const double dE = warp_sum(lane_tot - old_part);
         double tnew = s.toteng + dE;
-        if (!(tnew <= DBL_HUGE)) { tnew = DBL_HUGE; s.nclamp++; }  // Inf or NaN, :421-428
+        if (!(tnew <= DBL_HUGE)) { tnew = DBL_HUGE; nclamp++; }    // Inf or NaN, :421-428
 
         // ---- METROPOLIS (:720-788)
         const double delta = tnew - s.toteng;
-        const double exponent = -1.0 * delta * 1000.0 / rt;
-        double kans, rvv;
+        const double exponent = delta * neg_inv_rt;
+        bool accept;
         int used = 7;
-        if (exponent < -75.0) { kans = 0.0; rvv = 1.0; }
-        else if (exponent >= 0.0) { kans = 1.0; rvv = 0.0; }
-        else { kans = fmin(exp(exponent * LN_E_F32), 1.0); rvv = shfl_d(myu, 7); used = 8; }
-        const bool accept = rvv <= kans;
-        s.step++; s.uused += used; s.last_delta = delta;
-        s.sitepairs += (long long)(wpair * nn + wsol);
-        if (UBUF) cursor += used; else s.rng_n += used;
+        if (exponent < -75.0) accept = false;                       // KANS = 0, RV = 1, no draw
+        else if (exponent >= 0.0) accept = true;                    // KANS = 1, RV = 0, no draw
+        else { accept = shfl_d(myu, 7) <= fmin(exp(exponent * LN_E_F32), 1.0); used = 8; }
+        PH_T(3);
+        uused += used; s.last_delta = delta;
+        sitepairs += (unsigned)(wpair * nn + wsol);
+        if (UBUF) cursor += used;
+        const bool in_prod = (long long)(step0 + (unsigned)done + 1ULL) >= s.start_prod;
         if (accept) {
-            s.nsuc++; s.naccept++;
-            if (s.step >= s.start_prod) { s.production += tnew; s.prod_acc++; }
-            for (int j = lane; j < N; j += 32) {
-                double v = p.newrow[j];
-                if (MAT_SMEM || v != mat[(size_t)i * MS + j]) { mat[(size_t)i * MS + j] = v; mat[(size_t)j * MS + i] = v; }
-            }
+            nsuc++; nacc++;
+            if (in_prod) { s.production += tnew; prod_acc++; }
+            for (int j = lane; j < N; j += 32)
+                if (MAT_SMEM || mat[(size_t)i * MS + j] != 0.0) { mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0; }
             if (lane >= 1 && lane <= 6) base[i] = nv;
             if (lane < 4) {
-                p.sites[SITE_DOUBLES * i + 3 * a] = sx; p.sites[SITE_DOUBLES * i + 3 * a + 1] = sy;
-                p.sites[SITE_DOUBLES * i + 3 * a + 2] = sz;
+                sites[SITE_DOUBLES * i + 3 * a] = sx; sites[SITE_DOUBLES * i + 3 * a + 1] = sy;
+                sites[SITE_DOUBLES * i + 3 * a + 2] = sz;
             }
-            if (lane == 0) p.energy[i] = e_sol;
+            if (lane == 0) {   // ENERGY(i) = CalcLJ_SV: the solute slots
+                double es = 0.0;
+                for (int p = 0; p < nsolp; ++p) es += (epart[4 * p] + epart[4 * p + 1]) + (epart[4 * p + 2] + epart[4 * p + 3]);
+                energy[i] = es;
+            }
+            __syncwarp();
+            for (int sl = nsolp + lane; sl < nslots; sl += 32) {   // SS(i,j) = SS(j,i) = EN, :819-820
+                const int j = list[sl];
+                const double e = (epart[4 * sl] + epart[4 * sl + 1]) + (epart[4 * sl + 2] + epart[4 * sl + 3]);
+                mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
+            }
             s.toteng = tnew;
         }
-        if (s.step >= s.start_prod) { s.sum_e += s.toteng; s.sum_e2 = fma(s.toteng, s.toteng, s.sum_e2); s.nstat++; }
-        s.ratio = (double)((float)s.naccept / (float)s.nadj);       // default-REAL quotient, :758
+        if (in_prod) { s.sum_e += s.toteng; s.sum_e2 = fma(s.toteng, s.toteng, s.sum_e2); nstat++; }
+        racc = nacc;
         if (++adj_count == s.nadj) {                                // mod(I, NADJ) == 0, :766-777
             adj_count = 0;
-            if (s.ratio > 0.5) { s.dposmax *= (1.0 + s.padj); s.dhoekmax *= (1.0 + s.padj); }
-            else if (s.ratio < 0.5) { s.dposmax *= (1.0 - s.padj); s.dhoekmax *= (1.0 - s.padj); }
+            const double ratio = (double)((float)nacc / (float)s.nadj);   // default-REAL quotient, :758
+            if (ratio > 0.5) { s.dposmax *= (1.0 + s.padj); s.dhoekmax *= (1.0 + s.padj); }
+            else if (ratio < 0.5) { s.dposmax *= (1.0 - s.padj); s.dhoekmax *= (1.0 - s.padj); }
             s.dposmax = fmax(s.dposmax, s.dposmin); s.dhoekmax = fmax(s.dhoekmax, s.dhoekmin);
-            s.naccept = 0;
+            nacc = 0;
         }
         __syncwarp();
+        PH_T(4);
     }
+#ifdef MCB_PHASE_CLOCKS
+    if (lane == 0) for (int qq = 0; qq < 8; ++qq) atomicAdd(&g_phase[qq], (unsigned long long)ph[qq]);
+#endif
 
     // write back what can have changed: com, hoek, energy, solvent sites (contiguous) and the matrix
     {
         const int n_mut = g.o_sites + SITE_DOUBLES * N;
-        for (int q = lane; q < n_mut; q += 32) gimg[q] = img[q];
-        if (MAT_SMEM) for (int q = lane; q < N * MS; q += 32) gimg[g.o_mat + q] = img[g.o_mat + q];
+        for (int qq = lane; qq < n_mut; qq += 32) gimg[qq] = img[qq];
+        if (MAT_SMEM) for (int qq = lane; qq < N * MS; qq += 32) gimg[g.o_mat + qq] = img[g.o_mat + qq];
     }
     if (lane == 0) {
+        s.step += done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.uused += uused; s.prod_acc += prod_acc;
+        s.nstat += nstat; s.sitepairs += (long long)sitepairs;
+        // REAL(NACCEPT)/REAL(NADJ) as METROPOLIS leaves it after its last step (:758): before the window reset
+        if (done > 0) s.ratio = (double)((float)racc / (float)s.nadj);
         ctl[c] = s;
         if (out_consumed) out_consumed[c] = UBUF ? cursor : 0;
+        if (out_steps) out_steps[c] = done;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Batched mode with speculative look-ahead (built-in uniform stream only).
+//
+// One step of one chain is a long chain of dependent operations (~4000 cycles) around only ~230 site pairs, and
+// BASELINE's configuration fixes the number of chains, so a GPU full of one-warp-per-chain steps is latency-
+// bound at ~10 % of the fp64 pipe.  Here a warp works on T = 32/GL CONSECUTIVE steps of its chain at once, GL
+// lanes per step, all evaluated against the same committed state.  The stream is random-access (step s owns
+// u(8s..8s+7)), so the trial move of step k+g does not depend on the outcome of the steps before it.  After
+// the evaluation the steps are resolved in order: step k+g stands if every ACCEPTED earlier step of the batch
+// moved a molecule that step k+g never looked at — not the same molecule, not inside the cutoff of the trial
+// position (before or after its own move) and not a non-zero entry of the old matrix row (before or after).
+// The first step that fails the test, and everything behind it, is thrown away and re-evaluated in the next
+// batch with the same uniforms; a batch also ends at a step-size adaptation.  The resulting Markov chain is the
+// sequential one, decision for decision.  Only committed steps count as work.
+template <bool COUL, bool MAT_SMEM, int GL>
+__global__ void __launch_bounds__(32) k_run_spec(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl,
+                                                 long long nsteps, long long *out_steps)
+{
+    constexpr int T = 32 / GL;          // steps in flight
+    constexpr int NSUB = GL / 4;        // lanes of a group that share one own site
+    constexpr int MCH = 32 / GL;        // molecules per lane per 32-molecule chunk
+    constexpr unsigned GMASK = GL == 32 ? 0xffffffffu : ((1u << GL) - 1u);
+    static_assert(GL == 8 || GL == 16 || GL == 32, "a step needs 7 role lanes");
+    extern __shared__ __align__(16) double smem[];
+    const int lane = threadIdx.x;
+    const int c = blockIdx.x;
+    const int N = g.N, Np = g.Np, MS = g.MS, nsolp = g.nsolp;
+    double *gimg = images + (size_t)c * g.image_doubles;
+    double *img = smem;
+    {
+        const double2 *src = reinterpret_cast<const double2 *>(gimg);
+        double2 *dst = reinterpret_cast<double2 *>(img);
+        for (int k = lane; k < g.stage_doubles / 2; k += 32) dst[k] = src[k];
+    }
+    double *mat = MAT_SMEM ? img + g.o_mat : matg + (size_t)c * N * MS;
+    double *const com = img + g.o_com, *const hoek = img + g.o_hoek, *const energy = img + g.o_energy;
+    double *const sites = img + g.o_sites;
+    const double *const tabAB = img + g.o_tabAB, *const tabQ = img + g.o_tabQ;
+    const int grp = lane / GL, r = lane % GL, leader = grp * GL;
+    const int a = r & 3, sub = r >> 2;
+    double *const wk = smem + g.stage_doubles + (size_t)grp * g.spec_group_doubles;
+    int *const list = reinterpret_cast<int *>(wk + g.o_list);
+    double *const epart = wk + g.o_epart;
+    unsigned *const touch = reinterpret_cast<unsigned *>(wk + g.o_touch);
+    unsigned *const touch0 = reinterpret_cast<unsigned *>(smem + g.stage_doubles + g.o_touch);
+    ChainCtl s = ctl[c];
+    for (int p = r; p < nsolp; p += GL) list[p] = N + p;
+    __syncwarp();
+    {
+        double acc = 0.0;
+        for (int i = 0; i < N; ++i)
+            for (int j = i + 1 + lane; j < N; j += 32) acc += mat[(size_t)i * MS + j];
+        for (int i = lane; i < N; i += 32) acc += energy[i];
+        s.toteng = warp_sum(acc);
+    }
+    const double relx = rel.r[3 * a], rely = rel.r[3 * a + 1], relz = rel.r[3 * a + 2];
+    const int wpair = rel.n_sites * rel.n_sites, wsol = rel.n_sites * g.nsol;
+    const double neg_inv_rt = -1000.0 / (8.314 * s.temperature);
+    const int rr = min(max(r - 1, 0), 5);
+    const bool isang = rr >= 3;
+    const int k = isang ? rr - 3 : rr;
+    double *const base = (isang ? hoek : com) + k * Np;
+    const double period = isang ? TAU_D : g.boxl2, half = isang ? PI_D : g.boxl;
+    const double inv_half = isang ? 1.0 / PI_D : g.inv_boxl;
+    const double f1 = isang ? 1.0 : INV_SQRT3;
+    int adj_count = (int)(s.step % s.nadj);
+    int done = 0;
+    unsigned nsuc = 0, nacc = (unsigned)s.naccept, racc = 0, nclamp = 0, uused = 0, prod_acc = 0, nstat = 0;
+    unsigned long long sitepairs = 0;
+    const unsigned long long step0 = (unsigned long long)s.step;
+    const int nsteps_i = (int)min(nsteps, (long long)0x3fffffff);
+#ifdef MCB_PHASE_CLOCKS
+    long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tph = clock64();
+#endif
+
+    while (done < nsteps_i) {
+        // ================= evaluation of step (done + grp) by group grp =================
+        const double myu = stream_uniform(s.rng_key, 8ULL * (step0 + (unsigned)(done + grp)) + (unsigned)(r & 7));
+        const double u0 = shfl_d(myu, leader);
+        int i = (int)(u0 * (double)N) + 1;                          // MCINIT, MonteCarlo.F90:697-698
+        if (g.quirk31 && i == 31) i = 30;
+        i = min(i, N) - 1;
+        // old row of the pair matrix + ENERGY(i); its non-zero pattern is half of the "touch" set
+        double old_part = r == 0 ? energy[i] : 0.0;
+        for (int c0 = 0, w = 0; c0 < N; c0 += 32, ++w) {
+            unsigned word = 0;
+#pragma unroll
+            for (int m = 0; m < MCH; ++m) {
+                const int j = c0 + r + GL * m;
+                const double v = j < N ? mat[(size_t)i * MS + j] : 0.0;
+                old_part += v;
+                const unsigned b = __ballot_sync(FULL, v != 0.0);
+                word |= ((b >> leader) & GMASK) << (GL * m);
+            }
+            if (r == 0) touch[w] = word;
+        }
+        double rv = (myu - 0.5) * 2.0;                               // randVec / randVecHoek, lib.f90:111-131
+        rv = f1 * rv;
+        rv = (isang ? s.dhoekmax : s.dposmax) * rv;
+        const double nv = wrap_checked(base[i] + rv, period, half, inv_half);   // :699-712
+        double sn, cs;
+        sincos(nv, &sn, &cs);
+        const double ncx = shfl_d(nv, leader + 1), ncy = shfl_d(nv, leader + 2), ncz = shfl_d(nv, leader + 3);
+        const double c1 = shfl_d(cs, leader + 4), s1 = shfl_d(sn, leader + 4), c2 = shfl_d(cs, leader + 5),
+                     s2 = shfl_d(sn, leader + 5), c3 = shfl_d(cs, leader + 6), s3 = shfl_d(sn, leader + 6);
+        double sx, sy, sz;
+        rotate_site(c1, s1, c2, s2, c3, s3, relx, rely, relz, ncx, ncy, ncz, sx, sy, sz);
+        PH_T(0);
+        // centre-of-mass gate (:804-813): MCH partners per lane and chunk
+        int nn = 0;
+        __syncwarp();
+        for (int c0 = 0, w = 0; c0 < N; c0 += 32, ++w) {
+            unsigned word = 0;
+            bool in[MCH];
+#pragma unroll
+            for (int m = 0; m < MCH; ++m) {
+                const int j = c0 + r + GL * m;
+                in[m] = false;
+                if (j < N && j != i) {
+                    in[m] = !(pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2);
+                }
+                const unsigned b = __ballot_sync(FULL, in[m]);
+                word |= ((b >> leader) & GMASK) << (GL * m);
+            }
+#pragma unroll
+            for (int m = 0; m < MCH; ++m)
+                if (in[m]) list[nsolp + nn + __popc(word & ((1u << (r + GL * m)) - 1u))] = c0 + r + GL * m;
+            if (r == 0) touch[w] |= word;
+            nn += __popc(word);
+        }
+        __syncwarp();
+        PH_T(1);
+        // site pairs: lanes with the same own site split the slots; two items (8 site pairs) in flight
+        const int nslots = nsolp + nn;
+        double lane_tot = 0.0;
+        for (int s0 = sub; s0 < nslots; s0 += 2 * NSUB) {
+            const int sA = s0, sB = s0 + NSUB;
+            double eA = item_energy<COUL>(g, sites, tabAB, tabQ, list[sA], sA < nsolp ? 1 + sA : 0, a, sx, sy, sz);
+            double eB = 0.0;
+            if (sB < nslots) eB = item_energy<COUL>(g, sites, tabAB, tabQ, list[sB], sB < nsolp ? 1 + sB : 0, a, sx, sy, sz);
+            epart[4 * sA + a] = eA;
+            if (sB < nslots) epart[4 * sB + a] = eB;
+            lane_tot += eA + eB;
+        }
+        PH_T(2);
+        double dE = lane_tot - old_part;
+#pragma unroll
+        for (int o = GL / 2; o >= 1; o >>= 1) dE += shfl_xor_d(dE, o);
+        // METROPOLIS (:720-788) on DELTA = dE
+        const double exponent = dE * neg_inv_rt;
+        const double u7 = shfl_d(myu, leader + 7);                   // fetched by every lane: the branches below diverge between groups
+        bool accept, used8 = false;
+        if (!(fabs(dE) <= DBL_HUGE)) accept = false;                 // Inf/NaN trial energy: clamped, rejected (:421-428)
+        else if (exponent < -75.0) accept = false;
+        else if (exponent >= 0.0) accept = true;
+        else { accept = u7 <= fmin(exp(exponent * LN_E_F32), 1.0); used8 = true; }
+        const bool clamped = !(fabs(dE) <= DBL_HUGE);
+        PH_T(3);
+        // ================= resolution: which steps of the batch stand =================
+        const unsigned accmask = __ballot_sync(FULL, accept);
+        const unsigned u8mask = __ballot_sync(FULL, used8);
+        const unsigned clmask = __ballot_sync(FULL, clamped);
+        int limit = min(min(T, nsteps_i - done), s.nadj - adj_count);   // a batch never runs past an adaptation
+        int progress = 1;
+        unsigned acc_valid = (accmask >> 0) & 1u;
+        if (T > 1) {
+            unsigned depmask[T];
+            depmask[0] = 0;
+#pragma unroll
+            for (int gg = 1; gg < T; ++gg) {
+                const int ig = __shfl_sync(FULL, i, gg * GL);
+                const double bx = shfl_d(ncx, gg * GL), by = shfl_d(ncy, gg * GL), bz = shfl_d(ncz, gg * GL);
+                const double ox = com[ig], oy = com[Np + ig], oz = com[2 * Np + ig];
+                bool dep = false;
+                if (grp < gg) {   // my step is the earlier one: would its move (if accepted) change what step gg saw?
+                    dep = i == ig || ((touch0[(size_t)gg * g.spec_group_doubles * 2 + (i >> 5)] >> (i & 31)) & 1u);
+                    dep = dep || !(pair_r2(ncx - bx, ncy - by, ncz - bz, g) > g.cut2);
+                    dep = dep || !(pair_r2(ox - ncx, oy - ncy, oz - ncz, g) > g.cut2);
+                }
+                const unsigned b = __ballot_sync(FULL, dep);
+                unsigned dm = 0;
+#pragma unroll
+                for (int g2 = 0; g2 < T; ++g2) dm |= ((b >> (g2 * GL)) & 1u) << g2;
+                depmask[gg] = dm;
+            }
+#pragma unroll
+            for (int gg = 1; gg < T; ++gg) {
+                if (progress == gg && gg < limit && (depmask[gg] & acc_valid) == 0) {
+                    progress = gg + 1;
+                    acc_valid |= ((accmask >> (gg * GL)) & 1u) << gg;
+                }
+            }
+        }
+        (void)limit;
+        // ================= commit the accepted steps that stand (they are mutually independent) =================
+        const bool mine = grp < progress && accept;
+        if (mine) {
+            for (int c0 = 0; c0 < N; c0 += 32)
+#pragma unroll
+                for (int m = 0; m < MCH; ++m) {
+                    const int j = c0 + r + GL * m;
+                    if (j < N && (MAT_SMEM || mat[(size_t)i * MS + j] != 0.0)) { mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0; }
+                }
+            if (r >= 1 && r <= 6) base[i] = nv;
+            if (r < 4) {
+                sites[SITE_DOUBLES * i + 3 * a] = sx; sites[SITE_DOUBLES * i + 3 * a + 1] = sy;
+                sites[SITE_DOUBLES * i + 3 * a + 2] = sz;
+            }
+            if (r == 0) {
+                double es = 0.0;
+                for (int p = 0; p < nsolp; ++p) es += (epart[4 * p] + epart[4 * p + 1]) + (epart[4 * p + 2] + epart[4 * p + 3]);
+                energy[i] = es;
+            }
+        }
+        __syncwarp();
+        if (mine) {
+            for (int sl = nsolp + r; sl < nslots; sl += GL) {
+                const int j = list[sl];
+                const double e = (epart[4 * sl] + epart[4 * sl + 1]) + (epart[4 * sl + 2] + epart[4 * sl + 3]);
+                mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
+            }
+        }
+        // ================= bookkeeping in step order =================
+#pragma unroll
+        for (int gg = 0; gg < T; ++gg) {
+            const double dEg = shfl_d(dE, gg * GL);
+            const int nng = __shfl_sync(FULL, nn, gg * GL);
+            if (gg < progress) {
+                const bool accg = (accmask >> (gg * GL)) & 1u;
+                uused += 7 + ((u8mask >> (gg * GL)) & 1u);
+                nclamp += (clmask >> (gg * GL)) & 1u;
+                sitepairs += (unsigned)(wpair * nng + wsol);
+                s.last_delta = dEg;
+                const bool in_prod = (long long)(step0 + (unsigned)(done + gg) + 1ULL) >= s.start_prod;
+                if (accg) {
+                    nsuc++; nacc++;
+                    s.toteng += dEg;
+                    if (in_prod) { s.production += s.toteng; prod_acc++; }
+                }
+                if (in_prod) { s.sum_e += s.toteng; s.sum_e2 = fma(s.toteng, s.toteng, s.sum_e2); nstat++; }
+            }
+        }
+        racc = nacc;
+        adj_count += progress;
+        if (adj_count == s.nadj) {                                  // mod(I, NADJ) == 0, :766-777
+            adj_count = 0;
+            const double ratio = (double)((float)nacc / (float)s.nadj);
+            if (ratio > 0.5) { s.dposmax *= (1.0 + s.padj); s.dhoekmax *= (1.0 + s.padj); }
+            else if (ratio < 0.5) { s.dposmax *= (1.0 - s.padj); s.dhoekmax *= (1.0 - s.padj); }
+            s.dposmax = fmax(s.dposmax, s.dposmin); s.dhoekmax = fmax(s.dhoekmax, s.dhoekmin);
+            nacc = 0;
+        }
+        done += progress;
+        __syncwarp();
+        PH_T(4);
+    }
+#ifdef MCB_PHASE_CLOCKS
+    if (lane == 0) for (int qq = 0; qq < 8; ++qq) atomicAdd(&g_phase[qq], (unsigned long long)ph[qq]);
+#endif
+    {
+        const int n_mut = g.o_sites + SITE_DOUBLES * N;
+        for (int qq = lane; qq < n_mut; qq += 32) gimg[qq] = img[qq];
+        if (MAT_SMEM) for (int qq = lane; qq < N * MS; qq += 32) gimg[g.o_mat + qq] = img[g.o_mat + qq];
+    }
+    if (lane == 0) {
+        s.step += done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.uused += uused; s.prod_acc += prod_acc;
+        s.nstat += nstat; s.sitepairs += (long long)sitepairs;
+        if (done > 0) s.ratio = (double)((float)racc / (float)s.nadj);
+        ctl[c] = s;
         if (out_steps) out_steps[c] = done;
     }
 }

@@ -32,7 +32,7 @@ class McbError(RuntimeError):
 
 class LJEngine:
     def __init__(self, system, n_mol: int, n_chains: int = 1, device: int = -1, quirk_31: bool = True,
-                 matrix_mode: int = 0, with_solute: bool = True):
+                 matrix_mode: int = 0, with_solute: bool = True, lookahead: int = 0):
         self.lib = _lib.load()
         self.system = system
         self.n_mol, self.n_chains = int(n_mol), int(n_chains)
@@ -41,7 +41,7 @@ class LJEngine:
         self.n_sites = int(self._site_rel.shape[0])
         self.n_sol = int(system.solute.shape[0]) if with_solute else 0
         p = McbParams(n_mol=self.n_mol, n_sites=self.n_sites, n_sol=self.n_sol, n_chains=self.n_chains,
-                      device=device, quirk_31=1 if quirk_31 else 0, matrix_mode=matrix_mode, reserved=0,
+                      device=device, quirk_31=1 if quirk_31 else 0, matrix_mode=matrix_mode, lookahead=lookahead,
                       boxl=system.boxl, cutoff=system.cutoff, conv=system.conv,
                       site_rel=_d(self._site_rel), site_tab=_d(self._site_tab))
         self.h = C.c_void_p()

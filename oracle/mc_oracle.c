@@ -636,16 +636,23 @@ double mco_rng_uniform(uint64_t s[2])
     return (double)(x >> 11) * 0x1.0p-53;
 }
 
+/* u(n) of the stream, random access */
+static double rng_at(uint64_t key, uint64_t n)
+{
+    uint64_t x = mix64(key + (n + 1) * 0x9E3779B97F4A7C15ULL);
+    return (double)(x >> 11) * 0x1.0p-53;
+}
+
+/* Step s (0-based over the chain's life) owns u(8s)..u(8s+7): seven for MCINIT, the eighth only if METROPOLIS
+ * draws (MonteCarlo.F90:739).  rng[0] = key; rng[1] is set to the number of uniforms consumed so far. */
 int64_t mco_run_steps_rng(mco_chain *c, int64_t nsteps, uint64_t rng[2], double *trace)
 {
     double u[8];
     for (int64_t s = 0; s < nsteps; ++s) {
-        for (int k = 0; k < 7; ++k) u[k] = mco_rng_uniform(rng);
+        uint64_t base = 8ULL * (uint64_t)c->step;
+        for (int k = 0; k < 8; ++k) u[k] = rng_at(rng[0], base + k);
         int i = mco_mcinit(c, u);
-        /* the 8th uniform is drawn only when METROPOLIS needs it (MonteCarlo.F90:739) */
-        uint64_t save = rng[1];
-        u[7] = mco_rng_uniform(rng);
-        if (!finish_step(c, i, u + 7, trace ? trace + 10 * s : NULL)) rng[1] = save;
+        rng[1] += 7 + finish_step(c, i, u + 7, trace ? trace + 10 * s : NULL);
     }
     return nsteps;
 }

@@ -82,7 +82,7 @@ int mco_step_given_move(mco_chain *c, int i, const double new_com[3], const doub
 /* nsteps steps fed from a uniform buffer; stops early (returns steps done) if the buffer runs out */
 int64_t mco_run_steps(mco_chain *c, int64_t nsteps, const double *uniforms, int64_t cap, int64_t *consumed,
                       double *trace /* [nsteps][10] or NULL */);
-/* nsteps steps fed from the built-in counter-based stream (state advanced in place) */
+/* nsteps steps fed from the built-in counter stream: step s (0-based, chain life) owns u(8s)..u(8s+7) */
 int64_t mco_run_steps_rng(mco_chain *c, int64_t nsteps, uint64_t rng[2], double *trace);
 
 /* counters: {step, nsuc, naccept_window, prod_acc, n_clamped, sitepairs(lo), toteng, toteng_old, production,
