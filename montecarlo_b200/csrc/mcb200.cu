@@ -21,7 +21,9 @@ struct mcb_handle {
     Geo g{};
     SiteRel rel{};
     int n_chains = 0, device = 0, n_sites = 0;
-    bool coul = false, can_step = false, dirty = true;
+    bool coul = false, can_step = false, dirty = true, energy_only = false;
+    double *big_e = nullptr, *big_sol = nullptr, *big_out = nullptr; long long *big_n = nullptr, *big_nout = nullptr;
+    long long big_blocks = 0; int big_tiles = 0;
     cudaStream_t stream = nullptr;
     double *images = nullptr, *matg = nullptr, *work = nullptr;
     ChainCtl *ctl = nullptr;
@@ -112,6 +114,7 @@ extern "C" int mcb_destroy(mcb_t *h)
     cudaFree(h->images); cudaFree(h->matg); cudaFree(h->work); cudaFree(h->ctl);
     cudaFree(h->d_rsolv); cudaFree(h->d_vec); cudaFree(h->d_out); cudaFree(h->d_ll); cudaFree(h->d_acc);
     cudaFree(h->d_ubuf);
+    cudaFree(h->big_e); cudaFree(h->big_sol); cudaFree(h->big_out); cudaFree(h->big_n); cudaFree(h->big_nout);
     if (h->pin) cudaFreeHost(h->pin);
     delete h;
     return 0;
@@ -166,13 +169,25 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
     const size_t nc = (size_t)h->n_chains;
     CKC(cudaMalloc(&h->images, nc * g.image_doubles * sizeof(double)));
     CKC(cudaMemset(h->images, 0, nc * g.image_doubles * sizeof(double)));
-    if (!g.mat_in_image) {
+    // energy-only mode: a chain that does not fit in shared memory, or pair matrices that do not fit in HBM
+    // (BASELINE config 5).  Only mcb_total_energy (matrix-free kernels) is available then.
+    h->energy_only = !h->can_step;
+    if (!g.mat_in_image && !h->energy_only) {
         size_t bytes = nc * (size_t)g.N * g.MS * sizeof(double);
         size_t free_b = 0, total_b = 0;
         CKC(cudaMemGetInfo(&free_b, &total_b));
-        if (bytes > free_b / 2) { h->err = "mcb_create: pair matrices do not fit in device memory (n_chains * n_mol^2 too large)"; return fail(2); }
-        CKC(cudaMalloc(&h->matg, bytes));
-        CKC(cudaMemset(h->matg, 0, bytes));
+        if (bytes > free_b / 2) h->energy_only = true;
+        else { CKC(cudaMalloc(&h->matg, bytes)); CKC(cudaMemset(h->matg, 0, bytes)); }
+    }
+    if (h->energy_only) {
+        h->can_step = false;
+        h->big_tiles = (g.N + BIG_TILE - 1) / BIG_TILE;
+        h->big_blocks = (long long)h->big_tiles * (h->big_tiles + 1) / 2;
+        CKC(cudaMalloc(&h->big_e, sizeof(double) * h->big_blocks));
+        CKC(cudaMalloc(&h->big_n, sizeof(long long) * h->big_blocks));
+        CKC(cudaMalloc(&h->big_sol, sizeof(double) * h->big_tiles));
+        CKC(cudaMalloc(&h->big_out, sizeof(double) * 2));
+        CKC(cudaMalloc(&h->big_nout, sizeof(long long)));
     }
     CKC(cudaMalloc(&h->work, nc * g.work_doubles * sizeof(double)));
     CKC(cudaMemset(h->work, 0, nc * g.work_doubles * sizeof(double)));
@@ -316,10 +331,41 @@ static int launch_prepare(mcb_t *h, int chain0, int nchains, double *d_tot, doub
     return 0;
 }
 
+// matrix-free path: one chain at a time, partial sums through scratch (big_e / big_n / big_sol)
+static int big_energy(mcb_t *h, int c, double *tot, double *esol, long long *pairs)
+{
+    const Geo &g = h->g;
+    double *img = h->images + (size_t)c * g.image_doubles;
+    k_big_sites<<<h->big_tiles, BIG_TILE, 0, h->stream>>>(g, h->rel, img);
+    if (h->coul) {
+        k_big_pairs<true><<<(unsigned)h->big_blocks, BIG_TILE, 0, h->stream>>>(g, img, h->big_tiles, h->big_e, h->big_n);
+        k_big_solute<true><<<h->big_tiles, BIG_TILE, 0, h->stream>>>(g, img, h->big_sol);
+    } else {
+        k_big_pairs<false><<<(unsigned)h->big_blocks, BIG_TILE, 0, h->stream>>>(g, img, h->big_tiles, h->big_e, h->big_n);
+        k_big_solute<false><<<h->big_tiles, BIG_TILE, 0, h->stream>>>(g, img, h->big_sol);
+    }
+    k_big_reduce<<<1, BIG_TILE, 0, h->stream>>>(h->big_e, h->big_n, h->big_blocks, h->big_sol, h->big_tiles, h->big_out, h->big_nout);
+    h->launches += 4;
+    CK(h, cudaGetLastError());
+    double out[2]; long long n;
+    CK(h, cudaMemcpyAsync(out, h->big_out, sizeof(out), cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaMemcpyAsync(&n, h->big_nout, sizeof(n), cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    const double t = out[1] + out[0];
+    CK(h, cudaMemcpyAsync(reinterpret_cast<char *>(h->ctl + c) + offsetof(ChainCtl, toteng), &t, sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    if (tot) *tot = t;
+    if (esol) *esol = out[1];
+    if (pairs) *pairs = n;
+    return 0;
+}
+
 static int ensure_prepared(mcb_t *h)
 {
     if (!h->dirty) return 0;
-    if (int rc = launch_prepare(h, 0, h->n_chains, nullptr, nullptr, nullptr)) return rc;
+    if (h->energy_only) {
+        for (int c = 0; c < h->n_chains; ++c) if (int rc = big_energy(h, c, nullptr, nullptr, nullptr)) return rc;
+    } else if (int rc = launch_prepare(h, 0, h->n_chains, nullptr, nullptr, nullptr)) return rc;
     h->dirty = false;
     return 0;
 }
@@ -328,6 +374,15 @@ extern "C" int mcb_total_energy(mcb_t *h, int chain0, int nchains, double *toten
 {
     if (int rc = check_range(h, chain0, nchains)) return rc;
     CK(h, cudaSetDevice(h->device));
+    if (h->energy_only) {
+        for (int c = 0; c < nchains; ++c) {
+            long long n = 0;
+            if (int rc = big_energy(h, chain0 + c, toteng ? toteng + c : nullptr, e_solute_sum ? e_solute_sum + c : nullptr, &n)) return rc;
+            if (pairs_in_cutoff) pairs_in_cutoff[c] = n;
+        }
+        if (chain0 == 0 && nchains == h->n_chains) h->dirty = false;
+        return 0;
+    }
     double *d_tot = h->d_out, *d_esol = h->d_out + h->n_chains;
     if (int rc = launch_prepare(h, chain0, nchains, d_tot, d_esol, h->d_ll)) return rc;
     std::vector<long long> pairs(nchains);
@@ -343,6 +398,7 @@ extern "C" int mcb_total_energy(mcb_t *h, int chain0, int nchains, double *toten
 extern "C" int mcb_get_matrix(mcb_t *h, int chain, double *ss, double *energy)
 {
     if (int rc = check_range(h, chain, 1)) return rc;
+    if (h->energy_only) return arg_err(h, "mcb_get_matrix: this handle is in energy-only mode (no pair matrix is kept for a box this large)");
     if (int rc = ensure_prepared(h)) return rc;
     const Geo &g = h->g;
     const double *mat = g.mat_in_image ? h->images + (size_t)chain * g.image_doubles + g.o_mat : h->matg + (size_t)chain * g.N * g.MS;
@@ -368,6 +424,7 @@ extern "C" int mcb_trial_delta(mcb_t *h, int nchains, const int *rsolv, const do
 {
     if (int rc = check_range(h, 0, nchains)) return rc;
     if (!rsolv || !new_com || !new_hoek) return arg_err(h, "mcb_trial_delta: null array");
+    if (h->energy_only) return arg_err(h, "mcb_trial_delta: this handle is in energy-only mode (box too large for the stepping kernels)");
     for (int c = 0; c < nchains; ++c)
         if (rsolv[c] < 1 || rsolv[c] > h->g.N) return arg_err(h, "mcb_trial_delta: rsolv outside 1..n_mol");
     CK(h, cudaSetDevice(h->device));
@@ -387,6 +444,7 @@ extern "C" int mcb_commit(mcb_t *h, int nchains, const unsigned char *accept)
 {
     if (int rc = check_range(h, 0, nchains)) return rc;
     if (!accept) return arg_err(h, "mcb_commit: null array");
+    if (h->energy_only) return arg_err(h, "mcb_commit: this handle is in energy-only mode");
     CK(h, cudaSetDevice(h->device));
     CK(h, cudaMemcpyAsync(h->d_acc, accept, nchains, cudaMemcpyHostToDevice, h->stream));
     k_commit<<<nchains, 32, 0, h->stream>>>(h->g, h->images, h->matg, h->work, h->ctl, h->d_acc);
@@ -400,6 +458,7 @@ extern "C" int mcb_row_energy(mcb_t *h, int chain, int i, double *ss_row, double
 {
     if (int rc = check_range(h, chain, 1)) return rc;
     if (i < 1 || i > h->g.N) return arg_err(h, "mcb_row_energy: i outside 1..n_mol");
+    if (h->energy_only) return arg_err(h, "mcb_row_energy: this handle is in energy-only mode");
     CK(h, cudaSetDevice(h->device));
     if (int rc = ensure_prepared(h)) return rc;
     const Geo &g = h->g;

@@ -187,6 +187,84 @@ __device__ __forceinline__ double item_energy(const Geo &g, const double *sites,
     return ea + eb;
 }
 
+// NI (partner, own site) items = 4*NI site pairs evaluated STAGE BY STAGE (all differences, all minimum images,
+// all r^2, all reciprocals, ...) so that one warp keeps 4*NI independent fp64 chains in flight: a lone warp gets
+// 126 cycles per site pair with the pairs written one after the other, 87 with 8 and 63 with 16 staged
+// (profiles/pairbench_r01b.txt), and with ~1.75 warps per SM sub-partition that is what decides the step time.
+// Items past the end are computed on a valid slot and dropped.
+template <bool COUL, int NI>
+__device__ __forceinline__ double items_staged(const Geo &g, const double *sites, const double *tabAB, const double *tabQ,
+                                               const int *list, int nsolp, int nslots, int s0, int stride, int a,
+                                               double sx, double sy, double sz, double *epart)
+{
+    constexpr int NP = 4 * NI;
+    constexpr double M = 4503599627370496.0;   // 2^52
+    double ax[NP], ay[NP], az[NP];
+    int slot[NI];
+    bool valid[NI];
+#pragma unroll
+    for (int n = 0; n < NI; ++n) {
+        const int sl = s0 + n * stride;
+        valid[n] = sl < nslots;
+        slot[n] = valid[n] ? sl : s0;
+        const double2 *sp = reinterpret_cast<const double2 *>(sites + SITE_DOUBLES * list[slot[n]]);
+        const double2 v0 = sp[0], v1 = sp[1], v2 = sp[2], v3 = sp[3], v4 = sp[4], v5 = sp[5];
+        // R = mol2(J) - mol1(I) (LennardJones.f90:69); only |R| is needed
+        ax[4 * n + 0] = fabs(v0.x - sx); ay[4 * n + 0] = fabs(v0.y - sy); az[4 * n + 0] = fabs(v1.x - sz);
+        ax[4 * n + 1] = fabs(v1.y - sx); ay[4 * n + 1] = fabs(v2.x - sy); az[4 * n + 1] = fabs(v2.y - sz);
+        ax[4 * n + 2] = fabs(v3.x - sx); ay[4 * n + 2] = fabs(v3.y - sy); az[4 * n + 2] = fabs(v4.x - sz);
+        ax[4 * n + 3] = fabs(v4.y - sx); ay[4 * n + 3] = fabs(v5.x - sy); az[4 * n + 3] = fabs(v5.y - sz);
+    }
+    double tx[NP], ty[NP], tz[NP];
+#pragma unroll
+    for (int q = 0; q < NP; ++q) { tx[q] = __fma_rd(ax[q], g.inv_boxl, M); ty[q] = __fma_rd(ay[q], g.inv_boxl, M); tz[q] = __fma_rd(az[q], g.inv_boxl, M); }
+#pragma unroll
+    for (int q = 0; q < NP; ++q) { tx[q] -= M; ty[q] -= M; tz[q] -= M; }
+#pragma unroll
+    for (int q = 0; q < NP; ++q) { ax[q] = fma(-g.boxl2, tx[q], ax[q]); ay[q] = fma(-g.boxl2, ty[q], ay[q]); az[q] = fma(-g.boxl2, tz[q], az[q]); }
+    double r2[NP], y[NP], e[NP];
+#pragma unroll
+    for (int q = 0; q < NP; ++q) r2[q] = ax[q] * ax[q];
+#pragma unroll
+    for (int q = 0; q < NP; ++q) r2[q] = fma(ay[q], ay[q], r2[q]);
+#pragma unroll
+    for (int q = 0; q < NP; ++q) r2[q] = fma(az[q], az[q], r2[q]);
+    if (COUL) {
+#pragma unroll
+        for (int q = 0; q < NP; ++q) { y[q] = rsqrt(r2[q]); }
+    } else {
+#pragma unroll
+        for (int q = 0; q < NP; ++q) asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y[q]) : "d"(r2[q]));
+#pragma unroll
+        for (int q = 0; q < NP; ++q) e[q] = fma(-r2[q], y[q], 1.0);
+#pragma unroll
+        for (int q = 0; q < NP; ++q) e[q] = fma(e[q], e[q], e[q]);
+#pragma unroll
+        for (int q = 0; q < NP; ++q) y[q] = fma(y[q], e[q], y[q]);
+    }
+    double tot = 0.0;
+#pragma unroll
+    for (int n = 0; n < NI; ++n) {
+        const int t = slot[n] < nsolp ? 1 + slot[n] : 0;
+        const double2 *ab = reinterpret_cast<const double2 *>(tabAB) + (t * 4 + a) * 4;
+        double en = 0.0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int q = 4 * n + b;
+            const double2 pb = ab[b];
+            if (COUL) {
+                const double inv = y[q] * y[q], s6 = inv * inv * inv;
+                en = fma(s6, fma(pb.x, s6, -pb.y), fma(tabQ[(t * 4 + a) * 4 + b], y[q], en));
+            } else {
+                const double s6 = (y[q] * y[q]) * y[q];
+                en = fma(s6, fma(pb.x, s6, -pb.y), en);
+            }
+        }
+        if (valid[n]) { epart[4 * slot[n] + a] = en; tot += en; }
+    }
+    return tot;
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Batched mode: nsteps Metropolis steps of one chain per warp, the chain's image resident in shared memory.
 //   UBUF      uniforms come from a caller buffer [chain][cap] instead of the built-in counter stream
@@ -522,15 +600,9 @@ __global__ void __launch_bounds__(32) k_run_spec(Geo g, SiteRel rel, double *ima
         // site pairs: lanes with the same own site split the slots; two items (8 site pairs) in flight
         const int nslots = nsolp + nn;
         double lane_tot = 0.0;
-        for (int s0 = sub; s0 < nslots; s0 += 2 * NSUB) {
-            const int sA = s0, sB = s0 + NSUB;
-            double eA = item_energy<COUL>(g, sites, tabAB, tabQ, list[sA], sA < nsolp ? 1 + sA : 0, a, sx, sy, sz);
-            double eB = 0.0;
-            if (sB < nslots) eB = item_energy<COUL>(g, sites, tabAB, tabQ, list[sB], sB < nsolp ? 1 + sB : 0, a, sx, sy, sz);
-            epart[4 * sA + a] = eA;
-            if (sB < nslots) epart[4 * sB + a] = eB;
-            lane_tot += eA + eB;
-        }
+        constexpr int NI = GL == 32 ? 2 : 4;   // items per pass: 8 or 16 site pairs in flight per lane
+        for (int s0 = sub; s0 < nslots; s0 += NI * NSUB)
+            lane_tot += items_staged<COUL, NI>(g, sites, tabAB, tabQ, list, nsolp, nslots, s0, NSUB, a, sx, sy, sz, epart);
         PH_T(2);
         double dE = lane_tot - old_part;
 #pragma unroll
@@ -658,6 +730,126 @@ __global__ void __launch_bounds__(32) k_run_spec(Geo g, SiteRel rel, double *ima
         ctl[c] = s;
         if (out_steps) out_steps[c] = done;
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Matrix-free full-box energy for boxes whose N x N matrix cannot exist (BASELINE config 5: ~10^5 molecules; the
+// reference itself needs 2 x 82 GB there, MonteCarlo.F90:320-321).  Same numbers as the start-up recompute
+// (:357-364): every unordered pair inside the centre-of-mass cutoff once, the larger index as MOL1.
+//   k_big_sites   RotMatrix for every molecule -> site cache                      (1 thread / molecule)
+//   k_big_pairs   128 x 128 tiles of (j, i<j): gate on the centres of mass staged in shared memory, the rare hits
+//                 evaluated in place; each block leaves one partial energy + pair count in SCRATCH
+//   k_big_solute  ENERGY(i) for every molecule, block partials into SCRATCH
+//   k_big_reduce  fixed-order sum of the scratch partials (deterministic; no fp64 atomics)
+constexpr int BIG_TILE = 128;
+
+__global__ void __launch_bounds__(128) k_big_sites(Geo g, SiteRel rel, double *img)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= g.N) return;
+    const double *com = img + g.o_com, *hoek = img + g.o_hoek;
+    double *sites = img + g.o_sites;
+    double s1, c1, s2, c2, s3, c3;
+    sincos(hoek[j], &s1, &c1); sincos(hoek[g.Np + j], &s2, &c2); sincos(hoek[2 * g.Np + j], &s3, &c3);
+    const double cx = com[j], cy = com[g.Np + j], cz = com[2 * g.Np + j];
+    for (int a = 0; a < NSITE; ++a) {
+        double ox, oy, oz;
+        rotate_site(c1, s1, c2, s2, c3, s3, rel.r[3 * a], rel.r[3 * a + 1], rel.r[3 * a + 2], cx, cy, cz, ox, oy, oz);
+        sites[SITE_DOUBLES * j + 3 * a] = ox; sites[SITE_DOUBLES * j + 3 * a + 1] = oy; sites[SITE_DOUBLES * j + 3 * a + 2] = oz;
+    }
+}
+
+// fixed-order block sum (tree over shared memory): same result on every run
+__device__ __forceinline__ double block_sum_128(double v, double *sh)
+{
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 64; o >= 1; o >>= 1) {
+        if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    const double r = sh[0];
+    __syncthreads();
+    return r;
+}
+
+template <bool COUL>
+__global__ void __launch_bounds__(128) k_big_pairs(Geo g, const double *img, int ntiles, double *scratch_e, long long *scratch_n)
+{
+    __shared__ double sc[3][BIG_TILE];
+    __shared__ double red[BIG_TILE];
+    // linear block index -> tile pair (tj >= ti) of the lower triangle
+    const long long b = blockIdx.x;
+    int tj = (int)((sqrt(8.0 * (double)b + 1.0) - 1.0) * 0.5);
+    while ((long long)tj * (tj + 1) / 2 > b) --tj;
+    while ((long long)(tj + 1) * (tj + 2) / 2 <= b) ++tj;
+    const int ti = (int)(b - (long long)tj * (tj + 1) / 2);
+    (void)ntiles;
+    const double *com = img + g.o_com, *sites = img + g.o_sites, *tabAB = img + g.o_tabAB, *tabQ = img + g.o_tabQ;
+    const int i0 = ti * BIG_TILE, j = tj * BIG_TILE + threadIdx.x;
+    {
+        const int i = i0 + threadIdx.x;
+        const bool ok = i < g.N;
+        sc[0][threadIdx.x] = ok ? com[i] : 0.0; sc[1][threadIdx.x] = ok ? com[g.Np + i] : 0.0; sc[2][threadIdx.x] = ok ? com[2 * g.Np + i] : 0.0;
+    }
+    __syncthreads();
+    double e = 0.0;
+    long long np = 0;
+    if (j < g.N) {
+        const double cx = com[j], cy = com[g.Np + j], cz = com[2 * g.Np + j];
+        const int ni = min(BIG_TILE, min(g.N, j) - i0);      // partners i < j only
+        for (int k = 0; k < ni; ++k) {
+            // R = CoM(J) - CoM(I) with I = j (MOL1), J = i (MonteCarlo.F90:806-812)
+            if (pair_r2(sc[0][k] - cx, sc[1][k] - cy, sc[2][k] - cz, g) > g.cut2) continue;
+            ++np;
+            const double *s1 = sites + SITE_DOUBLES * (size_t)j, *s2 = sites + SITE_DOUBLES * (size_t)(i0 + k);
+            double en = 0.0;
+            for (int a = 0; a < NSITE; ++a)          // calcLJ: a outer over MOL1, bb inner over MOL2 (LennardJones.f90:65-79)
+                for (int bb = 0; bb < NSITE; ++bb)
+                    en = site_pair_acc<COUL>(en, s2[3 * bb] - s1[3 * a], s2[3 * bb + 1] - s1[3 * a + 1], s2[3 * bb + 2] - s1[3 * a + 2],
+                                             tabAB[(a * 4 + bb) * 2], tabAB[(a * 4 + bb) * 2 + 1], COUL ? tabQ[a * 4 + bb] : 0.0, g);
+            e += en;
+        }
+    }
+    const double be = block_sum_128(e, red);
+    const double bn = block_sum_128((double)np, red);
+    if (threadIdx.x == 0) { scratch_e[blockIdx.x] = be; scratch_n[blockIdx.x] = (long long)bn; }
+}
+
+template <bool COUL>
+__global__ void __launch_bounds__(128) k_big_solute(Geo g, double *img, double *scratch_e)
+{
+    __shared__ double red[BIG_TILE];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const double *sites = img + g.o_sites, *tabAB = img + g.o_tabAB, *tabQ = img + g.o_tabQ;
+    double e = 0.0;
+    if (i < g.N) {
+        const double *s1 = sites + SITE_DOUBLES * (size_t)i;
+        for (int a = 0; a < NSITE; ++a)              // CalcLJ_SV (LennardJones.f90:131-143)
+            for (int p = 0; p < g.nsolp; ++p) {
+                const double *s2 = sites + SITE_DOUBLES * (size_t)(g.N + p);
+                for (int bb = 0; bb < 4; ++bb) {
+                    const int t = ((1 + p) * 4 + a) * 4 + bb;
+                    e = site_pair_acc<COUL>(e, s2[3 * bb] - s1[3 * a], s2[3 * bb + 1] - s1[3 * a + 1], s2[3 * bb + 2] - s1[3 * a + 2],
+                                            tabAB[2 * t], tabAB[2 * t + 1], COUL ? tabQ[t] : 0.0, g);
+                }
+            }
+        img[g.o_energy + i] = e;
+    }
+    const double be = block_sum_128(e, red);
+    if (threadIdx.x == 0) scratch_e[blockIdx.x] = be;
+}
+
+// one block: out[0] = sum of pair partials, out[1] = sum of solute partials, n_out = pairs in cutoff
+__global__ void __launch_bounds__(128) k_big_reduce(const double *pair_e, const long long *pair_n, long long npair_blocks,
+                                                    const double *sol_e, int nsol_blocks, double *out, long long *n_out)
+{
+    __shared__ double red[BIG_TILE];
+    double e = 0.0, n = 0.0, es = 0.0;
+    for (long long k = threadIdx.x; k < npair_blocks; k += BIG_TILE) { e += pair_e[k]; n += (double)pair_n[k]; }
+    for (int k = threadIdx.x; k < nsol_blocks; k += BIG_TILE) es += sol_e[k];
+    const double te = block_sum_128(e, red), tn = block_sum_128(n, red), ts = block_sum_128(es, red);
+    if (threadIdx.x == 0) { out[0] = te; out[1] = ts; n_out[0] = (long long)tn; }
 }
 
 // ---------------------------------------------------------------------------------------------------------

@@ -85,6 +85,29 @@ def test_startup_replica_k5(shipped):
     assert abs((tot[0] - esol[0]) - g["sum_upper"]) <= 1e-9 * abs(tot[0])
 
 
+def test_config5_hundred_thousand_molecules(shipped):
+    """BASELINE config 5: 15x15x15 replica, N = 101 250, full-box energy only (the reference cannot run it: its two
+    N x N matrices would need 2 x 82 GB).  Matrix-free kernels against the cell-list oracle, which itself is
+    anchored by the reference binary at k = 1, 2, 5 (test_oracle_golden.py)."""
+    box, system = shipped
+    b = boxio.replicate(box, 15)
+    assert b.n == 101250 and abs(b.boxl - 116.758028502) < 1e-9
+    s15 = _sys_for(system, b)
+    eng = _engine(s15, b.n, n_chains=1)
+    eng.set_state(b.com, b.hoek)
+    tot, esol, pairs = eng.total_energy()
+    o = ol.OracleChain(s15, b.com, b.hoek, keep_matrix=False)
+    e, es, npair = o.total_energy_matrixfree(cells=True)
+    assert pairs[0] == npair and abs(tot[0] - e) <= RTOL * abs(e) and abs(esol[0] - es) <= RTOL * abs(es)
+    # a second call gives the same bits (fixed-order reductions, no atomics)
+    assert eng.total_energy()[0][0] == tot[0]
+    from montecarlo_b200.engine import McbError
+    with pytest.raises(McbError, match="energy-only"):
+        eng.run_steps(10)
+    with pytest.raises(McbError, match="energy-only"):
+        eng.matrix(0)
+
+
 def test_coulomb_path_when_conv_is_nonzero(shipped):
     """The reference's CONV is 0 (LennardJones.f90:57); the kernel still carries q1 q2 / r * conv."""
     box, system = shipped
