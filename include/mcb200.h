@@ -19,6 +19,7 @@
 #ifndef MCB200_H
 #define MCB200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -26,6 +27,8 @@ extern "C" {
 #endif
 
 #define MCB_MAX_SITES 4 /* interacting sites per solvent molecule (DMSO: S, C, C, O; H is skipped) */
+#define MCB_NOALLOC_MAX_MOL 32768 /* largest box mcb_box_energy_noalloc accepts (size of its fixed scratch array) */
+#define MCB_NOALLOC_MAX_SOL 24    /* most solute atoms mcb_box_energy_noalloc accepts (they travel as a kernel argument) */
 
 typedef struct mcb_handle mcb_t;
 
@@ -140,6 +143,25 @@ int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, int64_t cap,
 int mcb_get_stats(mcb_t *h, int chain0, int nchains, mcb_chain_stats *out);
 /* zero the counters (step, nsuc, production, ...) but keep coordinates, energies and step sizes */
 int mcb_reset_stats(mcb_t *h, int chain0, int nchains);
+
+/* ---- for hosts that must not allocate ---------------------------------------------------------------- */
+/* No counterpart in the reference (which never touches a GPU).  Same result as mcb_total_energy, for callers
+ * that cannot let a library allocate device memory: a driver whose own pool owns the whole GPU, a process under
+ * a fixed memory cap, a timing-critical loop that cannot take the device-wide stall of cudaMalloc.  It needs no
+ * handle and calls no cudaMalloc / cudaFree or any allocating routine; its only scratch (per-block partial sums)
+ * is a ~0.5 MB array built into the library, which every GPU that loads the library holds until exit.
+ *   p           n_mol <= MCB_NOALLOC_MAX_MOL, n_sol <= MCB_NOALLOC_MAX_SOL, else rc 2 and a message; n_chains,
+ *               quirk_31, matrix_mode, lookahead are ignored; device -1 = current device
+ *   d_com, d_hoek  DEVICE pointers, double[n_mol][3] (the driver's TYPE(vector) arrays, already on the GPU)
+ *   solute, sol_tab  HOST pointers, double[n_sol][3] (coordinates; q, eps, sigma), may be NULL when n_sol == 0
+ *   d_out       DEVICE pointer, double[3]: TOTENG, sum_i ENERGY(i), unordered CoM pairs inside the cutoff
+ *   cuda_stream the kernels are only enqueued there; the result is ready when the stream reaches that point
+ *   errbuf      optional buffer for the error text (there is no handle to ask)
+ * The first call on each device also looks up the scratch array's device address; make that call before any
+ * stream capture begins.  All calls share the scratch array: calls whose kernels could overlap on the GPU
+ * (different streams or host threads) race and must be serialised by the caller. */
+int mcb_box_energy_noalloc(const mcb_params *p, const double *d_com, const double *d_hoek, const double *solute,
+                           const double *sol_tab, double *d_out, void *cuda_stream, char *errbuf, size_t errbuf_len);
 
 /* ---- measurement ---------------------------------------------------------------------------------- */
 /* Independent DFMA chains on every SM for about `ms` milliseconds: the fp64 peak that the roofline

@@ -69,6 +69,8 @@ SIGNATURES = {
     "mcb_get_stats": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(McbChainStats)]),
     "mcb_reset_stats": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "mcb_measure_fp64_peak": (C.c_int, [C.c_int, C.c_double, _dp]),
+    "mcb_box_energy_noalloc": (C.c_int, [C.POINTER(McbParams), C.c_void_p, C.c_void_p, _dp, _dp, C.c_void_p, C.c_void_p,
+                                         C.c_char_p, C.c_size_t]),
 }
 
 

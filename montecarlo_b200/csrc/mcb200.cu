@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -666,3 +667,203 @@ extern "C" int mcb_debug_phase_clocks(unsigned long long *out, int reset)
     return 0;
 }
 #endif
+
+// ================================================================================================
+// mcb_box_energy_noalloc — full-box energy for callers that must not allocate device memory.
+//
+// Some hosts cannot let a library call cudaMalloc: a driver that has handed every byte of the GPU to its own
+// pool at start-up, a job running under a fixed per-process memory cap, or a timing-critical loop that cannot
+// afford the device-wide synchronisation an allocation implies.  For them this one entry point computes the
+// same number as mcb_total_energy's matrix-free path without creating a handle and without allocating
+// anything, on the device or through any library: the caller passes device pointers for the coordinates and
+// for the result, the small tables travel as kernel arguments, and the per-block partial sums — the only
+// scratch the computation needs — live in the fixed array below.  Because that array is part of the loaded
+// library, every GPU that loads libmcb200.so carries it (about 0.5 MB) until the process exits, and its size
+// is what limits the box: MCB_NOALLOC_MAX_MOL molecules, MCB_NOALLOC_MAX_SOL solute atoms.
+//
+// The array is shared by every call and keeps whatever the last call left in it.  Nothing in it has to start
+// at zero: each call writes every slot it later reads (one slot per tile pair / tile) before its own
+// reduction kernel reads them, in stream order.  Two calls whose kernels overlap on the GPU (different
+// streams, or several host threads) would write the same slots and race; callers must serialise them.
+// ================================================================================================
+namespace {
+
+constexpr int NA_MAX_TILES = (MCB_NOALLOC_MAX_MOL + BIG_TILE - 1) / BIG_TILE;
+constexpr int NA_MAX_BLOCKS = NA_MAX_TILES * (NA_MAX_TILES + 1) / 2;
+
+struct NaScratch {
+    double pair_e[NA_MAX_BLOCKS];
+    long long pair_n[NA_MAX_BLOCKS];
+    double sol_e[NA_MAX_TILES];
+};
+
+// In host code this name is only a stand-in for the symbol; the device address comes from cudaGetSymbolAddress.
+static __device__ __align__(256) NaScratch g_na_scratch;
+
+struct NaArgs {                          // everything small travels by value: no device buffer needed
+    int N, nsol, n_sites, pad;
+    double boxl2, inv_boxl, cut2;
+    double rel[NSITE * 3];
+    double ab0[NSITE * NSITE * 2], q0[NSITE * NSITE];                      // solvent-solvent (A,B), q q conv
+    double sol[MCB_NOALLOC_MAX_SOL * 3];
+    double sol_ab[NSITE * MCB_NOALLOC_MAX_SOL * 2], sol_q[NSITE * MCB_NOALLOC_MAX_SOL];
+};
+
+__device__ __forceinline__ Geo na_geo(const NaArgs &a)
+{
+    Geo g{};
+    g.boxl2 = a.boxl2; g.inv_boxl = a.inv_boxl; g.cut2 = a.cut2;
+    return g;
+}
+
+// RotMatrix of one molecule into registers (MC_lib/lib.f90:27-83); com/hoek are the driver's AoS arrays
+__device__ __forceinline__ void na_sites(const NaArgs &a, const double *com, const double *hoek, int j, double out[SITE_DOUBLES])
+{
+    double s1, c1, s2, c2, s3, c3;
+    sincos(hoek[3 * (size_t)j], &s1, &c1); sincos(hoek[3 * (size_t)j + 1], &s2, &c2); sincos(hoek[3 * (size_t)j + 2], &s3, &c3);
+    for (int k = 0; k < NSITE; ++k)
+        rotate_site(c1, s1, c2, s2, c3, s3, a.rel[3 * k], a.rel[3 * k + 1], a.rel[3 * k + 2], com[3 * (size_t)j], com[3 * (size_t)j + 1],
+                    com[3 * (size_t)j + 2], out[3 * k], out[3 * k + 1], out[3 * k + 2]);
+}
+
+template <bool COUL>
+__global__ void __launch_bounds__(128) k_na_pairs(NaArgs a, const double *com, const double *hoek, NaScratch *sc)
+{
+    __shared__ double scom[3][BIG_TILE];
+    __shared__ double red[BIG_TILE];
+    const Geo g = na_geo(a);
+    const long long b = blockIdx.x;
+    int tj = (int)((sqrt(8.0 * (double)b + 1.0) - 1.0) * 0.5);
+    while ((long long)tj * (tj + 1) / 2 > b) --tj;
+    while ((long long)(tj + 1) * (tj + 2) / 2 <= b) ++tj;
+    const int ti = (int)(b - (long long)tj * (tj + 1) / 2);
+    const int i0 = ti * BIG_TILE, j = tj * BIG_TILE + threadIdx.x;
+    {
+        const int i = i0 + threadIdx.x;
+        const bool ok = i < a.N;
+        scom[0][threadIdx.x] = ok ? com[3 * (size_t)i] : 0.0; scom[1][threadIdx.x] = ok ? com[3 * (size_t)i + 1] : 0.0;
+        scom[2][threadIdx.x] = ok ? com[3 * (size_t)i + 2] : 0.0;
+    }
+    __syncthreads();
+    double e = 0.0, np = 0.0;
+    if (j < a.N) {
+        double mine[SITE_DOUBLES], other[SITE_DOUBLES];
+        bool have_mine = false;
+        const double cx = com[3 * (size_t)j], cy = com[3 * (size_t)j + 1], cz = com[3 * (size_t)j + 2];
+        const int ni = min(BIG_TILE, min(a.N, j) - i0);
+        for (int k = 0; k < ni; ++k) {
+            if (pair_r2(scom[0][k] - cx, scom[1][k] - cy, scom[2][k] - cz, g) > g.cut2) continue;   // MonteCarlo.F90:806-813
+            np += 1.0;
+            if (!have_mine) { na_sites(a, com, hoek, j, mine); have_mine = true; }
+            na_sites(a, com, hoek, i0 + k, other);
+            double en = 0.0;
+            for (int p = 0; p < NSITE; ++p)          // larger index j is MOL1 (outer), i is MOL2 (inner), LennardJones.f90:65-79
+                for (int q = 0; q < NSITE; ++q)
+                    en = site_pair_acc<COUL>(en, other[3 * q] - mine[3 * p], other[3 * q + 1] - mine[3 * p + 1], other[3 * q + 2] - mine[3 * p + 2],
+                                             a.ab0[(p * 4 + q) * 2], a.ab0[(p * 4 + q) * 2 + 1], COUL ? a.q0[p * 4 + q] : 0.0, g);
+            e += en;
+        }
+    }
+    const double be = block_sum_128(e, red), bn = block_sum_128(np, red);
+    if (threadIdx.x == 0) { sc->pair_e[blockIdx.x] = be; sc->pair_n[blockIdx.x] = (long long)bn; }
+}
+
+template <bool COUL>
+__global__ void __launch_bounds__(128) k_na_solute(NaArgs a, const double *com, const double *hoek, NaScratch *sc)
+{
+    __shared__ double red[BIG_TILE];
+    const Geo g = na_geo(a);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    double e = 0.0;
+    if (i < a.N && a.nsol > 0) {
+        double mine[SITE_DOUBLES];
+        na_sites(a, com, hoek, i, mine);
+        for (int p = 0; p < a.n_sites; ++p)          // CalcLJ_SV, LennardJones.f90:131-143
+            for (int q = 0; q < a.nsol; ++q)
+                e = site_pair_acc<COUL>(e, a.sol[3 * q] - mine[3 * p], a.sol[3 * q + 1] - mine[3 * p + 1], a.sol[3 * q + 2] - mine[3 * p + 2],
+                                        a.sol_ab[(p * MCB_NOALLOC_MAX_SOL + q) * 2], a.sol_ab[(p * MCB_NOALLOC_MAX_SOL + q) * 2 + 1],
+                                        COUL ? a.sol_q[p * MCB_NOALLOC_MAX_SOL + q] : 0.0, g);
+    }
+    const double be = block_sum_128(e, red);
+    if (threadIdx.x == 0) sc->sol_e[blockIdx.x] = be;
+}
+
+__global__ void __launch_bounds__(128) k_na_reduce(const NaScratch *sc, int npair_blocks, int ntiles, double *out)
+{
+    __shared__ double red[BIG_TILE];
+    double e = 0.0, n = 0.0, es = 0.0;
+    for (int k = threadIdx.x; k < npair_blocks; k += BIG_TILE) { e += sc->pair_e[k]; n += (double)sc->pair_n[k]; }
+    for (int k = threadIdx.x; k < ntiles; k += BIG_TILE) es += sc->sol_e[k];
+    const double te = block_sum_128(e, red), tn = block_sum_128(n, red), ts = block_sum_128(es, red);
+    if (threadIdx.x == 0) { out[0] = ts + te; out[1] = ts; out[2] = tn; }
+}
+
+constexpr int NA_MAX_DEVICES = 64;
+NaScratch *g_na_ptr[NA_MAX_DEVICES];      // device address of g_na_scratch, looked up once per device
+std::mutex g_na_mutex;
+
+void na_msg(char *buf, size_t len, const char *msg)
+{
+    if (buf && len) { snprintf(buf, len, "%s", msg); }
+}
+
+}  // namespace
+
+extern "C" int mcb_box_energy_noalloc(const mcb_params *p, const double *d_com, const double *d_hoek, const double *solute,
+                                      const double *sol_tab, double *d_out, void *cuda_stream, char *errbuf, size_t errbuf_len)
+{
+    if (!p || !d_com || !d_hoek || !d_out || !p->site_rel || !p->site_tab) { na_msg(errbuf, errbuf_len, "mcb_box_energy_noalloc: null argument"); return 1; }
+    if (p->n_mol < 1 || p->n_mol > MCB_NOALLOC_MAX_MOL) {
+        na_msg(errbuf, errbuf_len, "mcb_box_energy_noalloc: n_mol outside 1..MCB_NOALLOC_MAX_MOL (32768): the fixed scratch array holds "
+                                   "one partial sum per 128x128 tile pair and cannot grow; use mcb_create + mcb_total_energy for larger boxes");
+        return 2;
+    }
+    if (p->n_sol < 0 || p->n_sol > MCB_NOALLOC_MAX_SOL || (p->n_sol > 0 && (!solute || !sol_tab))) {
+        na_msg(errbuf, errbuf_len, "mcb_box_energy_noalloc: n_sol outside 0..MCB_NOALLOC_MAX_SOL (24), or solute tables missing: "
+                                   "the solute travels as a kernel argument of fixed size");
+        return 2;
+    }
+    if (p->n_sites < 1 || p->n_sites > MCB_MAX_SITES || !(p->boxl > 0.0) || !(p->cutoff > 0.0)) {
+        na_msg(errbuf, errbuf_len, "mcb_box_energy_noalloc: bad parameter (1 <= n_sites <= 4; boxl, cutoff > 0)");
+        return 1;
+    }
+    int dev = 0;
+    cudaError_t e = p->device >= 0 ? cudaSetDevice(p->device) : cudaSuccess;
+    if (e == cudaSuccess) e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= NA_MAX_DEVICES) { na_msg(errbuf, errbuf_len, e != cudaSuccess ? cudaGetErrorString(e) : "device ordinal too large"); return -(int)(e != cudaSuccess ? e : cudaErrorInvalidDevice); }
+    NaScratch *sc = nullptr;
+    {   // set-up, once per device, with that device current: resolve the device address of the scratch symbol
+        std::lock_guard<std::mutex> lock(g_na_mutex);
+        if (!g_na_ptr[dev]) {
+            void *ptr = nullptr;
+            e = cudaGetSymbolAddress(&ptr, g_na_scratch);
+            if (e != cudaSuccess || !ptr) { na_msg(errbuf, errbuf_len, cudaGetErrorString(e)); return -(int)(e != cudaSuccess ? e : cudaErrorInvalidSymbol); }
+            g_na_ptr[dev] = static_cast<NaScratch *>(ptr);
+        }
+        sc = g_na_ptr[dev];
+    }
+    NaArgs a;
+    memset(&a, 0, sizeof(a));
+    a.N = p->n_mol; a.nsol = p->n_sol; a.n_sites = p->n_sites;
+    a.boxl2 = 2.0 * p->boxl; a.inv_boxl = 1.0 / p->boxl; a.cut2 = exact_cut2(p->cutoff);
+    double tab[NSITE * 3] = {0};
+    for (int s = 0; s < p->n_sites; ++s)
+        for (int k = 0; k < 3; ++k) { a.rel[3 * s + k] = p->site_rel[3 * s + k]; tab[3 * s + k] = p->site_tab[3 * s + k]; }
+    for (int s = p->n_sites; s < NSITE; ++s) { a.rel[3 * s] = 1.0e4 + 7.0 * s; a.rel[3 * s + 1] = 2.0e4; a.rel[3 * s + 2] = 3.0e4; }   // parameter-free padding
+    for (int s = 0; s < p->n_sites; ++s) {
+        for (int t = 0; t < p->n_sites; ++t)
+            pair_consts(&tab[3 * s], &tab[3 * t], p->conv, a.ab0[(s * 4 + t) * 2], a.ab0[(s * 4 + t) * 2 + 1], a.q0[s * 4 + t]);
+        for (int q = 0; q < p->n_sol; ++q)
+            pair_consts(&tab[3 * s], sol_tab + 3 * q, p->conv, a.sol_ab[(s * MCB_NOALLOC_MAX_SOL + q) * 2],
+                        a.sol_ab[(s * MCB_NOALLOC_MAX_SOL + q) * 2 + 1], a.sol_q[s * MCB_NOALLOC_MAX_SOL + q]);
+    }
+    for (int q = 0; q < 3 * p->n_sol; ++q) a.sol[q] = solute[q];
+    const int tiles = (a.N + BIG_TILE - 1) / BIG_TILE, blocks = tiles * (tiles + 1) / 2;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    if (p->conv != 0.0) { k_na_pairs<true><<<blocks, BIG_TILE, 0, st>>>(a, d_com, d_hoek, sc); k_na_solute<true><<<tiles, BIG_TILE, 0, st>>>(a, d_com, d_hoek, sc); }
+    else { k_na_pairs<false><<<blocks, BIG_TILE, 0, st>>>(a, d_com, d_hoek, sc); k_na_solute<false><<<tiles, BIG_TILE, 0, st>>>(a, d_com, d_hoek, sc); }
+    k_na_reduce<<<1, BIG_TILE, 0, st>>>(sc, blocks, tiles, d_out);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) { na_msg(errbuf, errbuf_len, cudaGetErrorString(e)); return -(int)e; }
+    return 0;
+}
