@@ -36,7 +36,7 @@ struct mcb_handle {
     std::vector<double> tab0AB, tab0Q;                // type-0 tables
     long long launches = 0;
     size_t smem_bytes = 0, smem_spec_bytes = 0;
-    int lookahead = 4;
+    int lookahead = 4, spec_w = 1, spec_gl = 32;
     std::string err;
 };
 
@@ -94,15 +94,28 @@ static void setup_geo(mcb_handle *h)
     g.spec_group_doubles = g.work_doubles;
     size_t with_mat = round_up((size_t)end_tab + (size_t)g.N * g.MS, 2);
     // the matrix rides in shared memory while a chain's footprint leaves room for >= 7 chains per SM
-    bool mat_smem = p.matrix_mode != 1 && (with_mat + 4 * (size_t)g.work_doubles) * 8 <= 32 * 1024;
+    bool mat_smem = p.matrix_mode != 1 && (with_mat + 4 * (size_t)(g.work_doubles + SPECX_DOUBLES)) * 8 <= 32 * 1024;
     g.mat_in_image = mat_smem ? 1 : 0;
     g.image_doubles = (int)(mat_smem ? with_mat : (size_t)end_tab);
     g.stage_doubles = g.image_doubles;
     g.quirk31 = p.quirk_31;
     g.boxl = p.boxl; g.boxl2 = p.boxl * 2.0; g.inv_boxl = 1.0 / p.boxl; g.cut2 = exact_cut2(p.cutoff); g.conv = p.conv;
-    h->lookahead = p.lookahead == 1 || p.lookahead == 2 || p.lookahead == 4 ? p.lookahead : 2;
+    // steps in flight per chain -> (warps per chain, lanes per step); MCB200_TUNE="W,GL" overrides (tuning only)
+    h->lookahead = p.lookahead == 1 || p.lookahead == 2 || p.lookahead == 4 || p.lookahead == 8 ? p.lookahead : 2;
+    switch (h->lookahead) {   // measured on configs[1] (profiles/tune_r01*.txt): sharing a warp between two steps wins
+        case 1: h->spec_w = 1; h->spec_gl = 32; break;
+        case 4: h->spec_w = 1; h->spec_gl = 8; break;
+        case 8: h->spec_w = 2; h->spec_gl = 8; break;
+        default: h->spec_w = 1; h->spec_gl = 16; break;
+    }
+    if (const char *t = getenv("MCB200_TUNE")) {
+        int w = 0, gl = 0;
+        if (sscanf(t, "%d,%d", &w, &gl) == 2 && (w == 1 || w == 2 || w == 4) && (gl == 8 || gl == 16 || gl == 32) && w * 32 / gl <= 8) {
+            h->spec_w = w; h->spec_gl = gl; h->lookahead = w * 32 / gl;
+        }
+    }
     h->smem_bytes = ((size_t)g.stage_doubles + g.work_doubles) * 8;
-    h->smem_spec_bytes = ((size_t)g.stage_doubles + (size_t)h->lookahead * g.work_doubles) * 8;
+    h->smem_spec_bytes = ((size_t)g.stage_doubles + (size_t)h->lookahead * (g.work_doubles + SPECX_DOUBLES) + 2) * 8;
     h->can_step = h->smem_spec_bytes <= 227 * 1024;
 }
 
@@ -216,9 +229,9 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
         int rc = 0;
         rc |= set_smem_attr(h, k_run_steps<false, true, false>, h->smem_bytes); rc |= set_smem_attr(h, k_run_steps<false, true, true>, h->smem_bytes);
         rc |= set_smem_attr(h, k_run_steps<true, true, false>, h->smem_bytes);  rc |= set_smem_attr(h, k_run_steps<true, true, true>, h->smem_bytes);
-#define SPEC_ATTR(GL) rc |= set_smem_attr(h, k_run_spec<false, false, GL>, h->smem_spec_bytes); rc |= set_smem_attr(h, k_run_spec<false, true, GL>, h->smem_spec_bytes); \
-                      rc |= set_smem_attr(h, k_run_spec<true, false, GL>, h->smem_spec_bytes);  rc |= set_smem_attr(h, k_run_spec<true, true, GL>, h->smem_spec_bytes);
-        SPEC_ATTR(8) SPEC_ATTR(16) SPEC_ATTR(32)
+#define SPEC_ATTR(GL, W) rc |= set_smem_attr(h, k_run_spec<false, false, GL, W>, h->smem_spec_bytes); rc |= set_smem_attr(h, k_run_spec<false, true, GL, W>, h->smem_spec_bytes); \
+                         rc |= set_smem_attr(h, k_run_spec<true, false, GL, W>, h->smem_spec_bytes);  rc |= set_smem_attr(h, k_run_spec<true, true, GL, W>, h->smem_spec_bytes);
+        SPEC_ATTR(32, 1) SPEC_ATTR(32, 2) SPEC_ATTR(32, 4) SPEC_ATTR(16, 1) SPEC_ATTR(16, 2) SPEC_ATTR(16, 4) SPEC_ATTR(8, 1) SPEC_ATTR(8, 2)
 #undef SPEC_ATTR
         if (rc) return fail(rc);
     }
@@ -565,21 +578,29 @@ static void launch_run_ubuf(mcb_t *h, long long nsteps, long long cap, long long
         k_run_steps<COUL, true, false><<<h->n_chains, 32, h->smem_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, h->d_ubuf, cap, d_consumed, d_steps);
 }
 
-template <bool COUL, int GL>
+template <bool COUL, int GL, int W>
 static void launch_run_spec(mcb_t *h, long long nsteps, long long *d_steps)
 {
     if (h->g.mat_in_image)
-        k_run_spec<COUL, true, GL><<<h->n_chains, 32, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps);
+        k_run_spec<COUL, true, GL, W><<<h->n_chains, 32 * W, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps);
     else
-        k_run_spec<COUL, false, GL><<<h->n_chains, 32, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps);
+        k_run_spec<COUL, false, GL, W><<<h->n_chains, 32 * W, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps);
 }
 
 template <bool COUL>
 static void launch_run_spec_any(mcb_t *h, long long nsteps, long long *d_steps)
 {
-    if (h->lookahead == 4) launch_run_spec<COUL, 8>(h, nsteps, d_steps);
-    else if (h->lookahead == 2) launch_run_spec<COUL, 16>(h, nsteps, d_steps);
-    else launch_run_spec<COUL, 32>(h, nsteps, d_steps);
+    const int key = h->spec_gl * 10 + h->spec_w;
+    switch (key) {
+        case 321: launch_run_spec<COUL, 32, 1>(h, nsteps, d_steps); break;
+        case 322: launch_run_spec<COUL, 32, 2>(h, nsteps, d_steps); break;
+        case 324: launch_run_spec<COUL, 32, 4>(h, nsteps, d_steps); break;
+        case 161: launch_run_spec<COUL, 16, 1>(h, nsteps, d_steps); break;
+        case 162: launch_run_spec<COUL, 16, 2>(h, nsteps, d_steps); break;
+        case 164: launch_run_spec<COUL, 16, 4>(h, nsteps, d_steps); break;
+        case 81: launch_run_spec<COUL, 8, 1>(h, nsteps, d_steps); break;
+        default: launch_run_spec<COUL, 8, 2>(h, nsteps, d_steps); break;
+    }
 }
 
 extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, int64_t cap, int64_t *consumed, int64_t *steps_done)

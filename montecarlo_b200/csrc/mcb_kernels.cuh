@@ -468,28 +468,33 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
 // ---------------------------------------------------------------------------------------------------------
 // Batched mode with speculative look-ahead (built-in uniform stream only).
 //
-// One step of one chain is a long chain of dependent operations (~4000 cycles) around only ~230 site pairs, and
+// One step of one chain is a long chain of dependent operations (~3500 cycles) around only ~230 site pairs, and
 // BASELINE's configuration fixes the number of chains, so a GPU full of one-warp-per-chain steps is latency-
-// bound at ~10 % of the fp64 pipe.  Here a warp works on T = 32/GL CONSECUTIVE steps of its chain at once, GL
-// lanes per step, all evaluated against the same committed state.  The stream is random-access (step s owns
-// u(8s..8s+7)), so the trial move of step k+g does not depend on the outcome of the steps before it.  After
-// the evaluation the steps are resolved in order: step k+g stands if every ACCEPTED earlier step of the batch
-// moved a molecule that step k+g never looked at — not the same molecule, not inside the cutoff of the trial
-// position (before or after its own move) and not a non-zero entry of the old matrix row (before or after).
-// The first step that fails the test, and everything behind it, is thrown away and re-evaluated in the next
-// batch with the same uniforms; a batch also ends at a step-size adaptation.  The resulting Markov chain is the
-// sequential one, decision for decision.  Only committed steps count as work.
-template <bool COUL, bool MAT_SMEM, int GL>
-__global__ void __launch_bounds__(32) k_run_spec(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl,
-                                                 long long nsteps, long long *out_steps)
+// bound at ~12 % of the fp64 pipe.  Here a BLOCK of W warps works on T = W*32/GL CONSECUTIVE steps of its chain
+// at once, GL lanes per step, all evaluated against the same committed state.  The stream is random-access
+// (step s owns u(8s..8s+7)), so the trial move of step k+g does not depend on the outcome of the steps before
+// it.  After the evaluation the steps are resolved in order: step k+g stands if every ACCEPTED earlier step of
+// the batch moved a molecule that step k+g never looked at — not the same molecule, not inside the cutoff of the
+// trial position (before or after its own move) and not a non-zero entry of the old matrix row (before or
+// after).  The first step that fails the test, and everything behind it, is thrown away and re-evaluated in the
+// next batch with the same uniforms; a batch also ends at a step-size adaptation.  The resulting Markov chain
+// is the sequential one, decision for decision.  Only committed steps count as work.
+struct SpecX { double dE, esol, ncx, ncy, ncz; int i, nn, flags, pad; };   // what a step hands to the resolution
+constexpr int SPECX_DOUBLES = sizeof(SpecX) / 8;
+
+template <bool COUL, bool MAT_SMEM, int GL, int W>
+__global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl,
+                                                     long long nsteps, long long *out_steps)
 {
-    constexpr int T = 32 / GL;          // steps in flight
+    constexpr int G = 32 / GL;          // steps per warp
+    constexpr int T = W * G;            // steps in flight per chain
     constexpr int NSUB = GL / 4;        // lanes of a group that share one own site
     constexpr int MCH = 32 / GL;        // molecules per lane per 32-molecule chunk
     constexpr unsigned GMASK = GL == 32 ? 0xffffffffu : ((1u << GL) - 1u);
     static_assert(GL == 8 || GL == 16 || GL == 32, "a step needs 7 role lanes");
+    static_assert(T <= 8, "the resolution handles at most 8 steps (28 ordered pairs, one per lane)");
     extern __shared__ __align__(16) double smem[];
-    const int lane = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int c = blockIdx.x;
     const int N = g.N, Np = g.Np, MS = g.MS, nsolp = g.nsolp;
     double *gimg = images + (size_t)c * g.image_doubles;
@@ -497,22 +502,24 @@ __global__ void __launch_bounds__(32) k_run_spec(Geo g, SiteRel rel, double *ima
     {
         const double2 *src = reinterpret_cast<const double2 *>(gimg);
         double2 *dst = reinterpret_cast<double2 *>(img);
-        for (int k = lane; k < g.stage_doubles / 2; k += 32) dst[k] = src[k];
+        for (int k = tid; k < g.stage_doubles / 2; k += 32 * W) dst[k] = src[k];
     }
     double *mat = MAT_SMEM ? img + g.o_mat : matg + (size_t)c * N * MS;
     double *const com = img + g.o_com, *const hoek = img + g.o_hoek, *const energy = img + g.o_energy;
     double *const sites = img + g.o_sites;
     const double *const tabAB = img + g.o_tabAB, *const tabQ = img + g.o_tabQ;
     const int grp = lane / GL, r = lane % GL, leader = grp * GL;
+    const int gidx = warp * G + grp;    // which step of the batch this group evaluates
     const int a = r & 3, sub = r >> 2;
-    double *const wk = smem + g.stage_doubles + (size_t)grp * g.spec_group_doubles;
+    double *const wk0 = smem + g.stage_doubles;
+    double *const wk = wk0 + (size_t)gidx * g.spec_group_doubles;
     int *const list = reinterpret_cast<int *>(wk + g.o_list);
     double *const epart = wk + g.o_epart;
     unsigned *const touch = reinterpret_cast<unsigned *>(wk + g.o_touch);
-    unsigned *const touch0 = reinterpret_cast<unsigned *>(smem + g.stage_doubles + g.o_touch);
+    SpecX *const xch = reinterpret_cast<SpecX *>(wk0 + (size_t)T * g.spec_group_doubles);
     ChainCtl s = ctl[c];
     for (int p = r; p < nsolp; p += GL) list[p] = N + p;
-    __syncwarp();
+    __syncthreads();
     {
         double acc = 0.0;
         for (int i = 0; i < N; ++i)
@@ -530,6 +537,10 @@ __global__ void __launch_bounds__(32) k_run_spec(Geo g, SiteRel rel, double *ima
     const double period = isang ? TAU_D : g.boxl2, half = isang ? PI_D : g.boxl;
     const double inv_half = isang ? 1.0 / PI_D : g.inv_boxl;
     const double f1 = isang ? 1.0 : INV_SQRT3;
+    // which ordered pair (ga < gb) of steps this lane checks in the resolution
+    int gb = 1;
+    while (gb * (gb + 1) / 2 <= lane) ++gb;
+    const int ga = lane - gb * (gb - 1) / 2;
     int adj_count = (int)(s.step % s.nadj);
     int done = 0;
     unsigned nsuc = 0, nacc = (unsigned)s.naccept, racc = 0, nclamp = 0, uused = 0, prod_acc = 0, nstat = 0;
@@ -541,14 +552,18 @@ __global__ void __launch_bounds__(32) k_run_spec(Geo g, SiteRel rel, double *ima
 #endif
 
     while (done < nsteps_i) {
-        // ================= evaluation of step (done + grp) by group grp =================
-        const double myu = stream_uniform(s.rng_key, 8ULL * (step0 + (unsigned)(done + grp)) + (unsigned)(r & 7));
+        // ================= evaluation of step (done + gidx) by this group =================
+        const double myu = stream_uniform(s.rng_key, 8ULL * (step0 + (unsigned)(done + gidx)) + (unsigned)(r & 7));
         const double u0 = shfl_d(myu, leader);
+        // METROPOLIS draws RV <= E**x; with x < 0 that is log(RV)/log(E) <= x.  The left side only needs the uniform,
+        // so it is ready long before dE is.
+        const double thr = shfl_d(log(myu) * (1.0 / LN_E_F32), leader + 7);
         int i = (int)(u0 * (double)N) + 1;                          // MCINIT, MonteCarlo.F90:697-698
         if (g.quirk31 && i == 31) i = 30;
         i = min(i, N) - 1;
         // old row of the pair matrix + ENERGY(i); its non-zero pattern is half of the "touch" set
         double old_part = r == 0 ? energy[i] : 0.0;
+        unsigned oldw0 = 0;
         for (int c0 = 0, w = 0; c0 < N; c0 += 32, ++w) {
             unsigned word = 0;
 #pragma unroll
@@ -559,7 +574,7 @@ __global__ void __launch_bounds__(32) k_run_spec(Geo g, SiteRel rel, double *ima
                 const unsigned b = __ballot_sync(FULL, v != 0.0);
                 word |= ((b >> leader) & GMASK) << (GL * m);
             }
-            if (r == 0) touch[w] = word;
+            if (w == 0) oldw0 = word; else if (r == 0) touch[w] = word;
         }
         double rv = (myu - 0.5) * 2.0;                               // randVec / randVecHoek, lib.f90:111-131
         rv = f1 * rv;
@@ -575,7 +590,7 @@ __global__ void __launch_bounds__(32) k_run_spec(Geo g, SiteRel rel, double *ima
         PH_T(0);
         // centre-of-mass gate (:804-813): MCH partners per lane and chunk
         int nn = 0;
-        __syncwarp();
+        unsigned neww0 = 0;
         for (int c0 = 0, w = 0; c0 < N; c0 += 32, ++w) {
             unsigned word = 0;
             bool in[MCH];
@@ -583,119 +598,115 @@ __global__ void __launch_bounds__(32) k_run_spec(Geo g, SiteRel rel, double *ima
             for (int m = 0; m < MCH; ++m) {
                 const int j = c0 + r + GL * m;
                 in[m] = false;
-                if (j < N && j != i) {
-                    in[m] = !(pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2);
-                }
+                if (j < N && j != i) in[m] = !(pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2);
                 const unsigned b = __ballot_sync(FULL, in[m]);
                 word |= ((b >> leader) & GMASK) << (GL * m);
             }
 #pragma unroll
             for (int m = 0; m < MCH; ++m)
                 if (in[m]) list[nsolp + nn + __popc(word & ((1u << (r + GL * m)) - 1u))] = c0 + r + GL * m;
-            if (r == 0) touch[w] |= word;
+            if (w == 0) { neww0 = word; if (r == 0) touch[0] = oldw0 | word; }
+            else if (r == 0) touch[w] |= word;
             nn += __popc(word);
         }
         __syncwarp();
         PH_T(1);
-        // site pairs: lanes with the same own site split the slots; two items (8 site pairs) in flight
+        // site pairs: lanes with the same own site split the slots; NI items staged per pass
         const int nslots = nsolp + nn;
         double lane_tot = 0.0;
-        constexpr int NI = GL == 32 ? 2 : 4;   // items per pass: 8 or 16 site pairs in flight per lane
+        constexpr int NI = GL == 32 ? 2 : 4;   // (a shorter tail pass was tried: the extra code paths cost more than they saved)
         for (int s0 = sub; s0 < nslots; s0 += NI * NSUB)
             lane_tot += items_staged<COUL, NI>(g, sites, tabAB, tabQ, list, nsolp, nslots, s0, NSUB, a, sx, sy, sz, epart);
         PH_T(2);
+        // dE = sum(new row) - sum(old row) over the group; ENERGY(i) = the solute slots' share of it
         double dE = lane_tot - old_part;
+        double esol = 0.0;
+        __syncwarp();
+        for (int p = sub; p < nsolp; p += NSUB) esol += epart[4 * p + a];
 #pragma unroll
-        for (int o = GL / 2; o >= 1; o >>= 1) dE += shfl_xor_d(dE, o);
+        for (int o = GL / 2; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
         // METROPOLIS (:720-788) on DELTA = dE
         const double exponent = dE * neg_inv_rt;
-        const double u7 = shfl_d(myu, leader + 7);                   // fetched by every lane: the branches below diverge between groups
-        bool accept, used8 = false;
-        if (!(fabs(dE) <= DBL_HUGE)) accept = false;                 // Inf/NaN trial energy: clamped, rejected (:421-428)
-        else if (exponent < -75.0) accept = false;
-        else if (exponent >= 0.0) accept = true;
-        else { accept = u7 <= fmin(exp(exponent * LN_E_F32), 1.0); used8 = true; }
-        const bool clamped = !(fabs(dE) <= DBL_HUGE);
+        const bool clamped = !(fabs(dE) <= DBL_HUGE);                // Inf/NaN trial energy: clamped, rejected (:421-428)
+        const bool used8 = !clamped && exponent >= -75.0 && exponent < 0.0;
+        const bool accept = !clamped && (exponent >= 0.0 || (used8 && thr <= exponent));
+        if (r == 0) {
+            SpecX x;
+            x.dE = dE; x.esol = esol; x.ncx = ncx; x.ncy = ncy; x.ncz = ncz; x.i = i; x.nn = nn;
+            x.flags = (accept ? 1 : 0) | (used8 ? 2 : 0) | (clamped ? 4 : 0); x.pad = 0;
+            xch[gidx] = x;
+        }
         PH_T(3);
-        // ================= resolution: which steps of the batch stand =================
-        const unsigned accmask = __ballot_sync(FULL, accept);
-        const unsigned u8mask = __ballot_sync(FULL, used8);
-        const unsigned clmask = __ballot_sync(FULL, clamped);
-        int limit = min(min(T, nsteps_i - done), s.nadj - adj_count);   // a batch never runs past an adaptation
+        if (W > 1) __syncthreads(); else __syncwarp();
+        // ================= resolution (every warp, redundantly): which steps of the batch stand =================
+        const int limit = min(min(T, nsteps_i - done), s.nadj - adj_count);   // a batch never runs past an adaptation
         int progress = 1;
-        unsigned acc_valid = (accmask >> 0) & 1u;
         if (T > 1) {
-            unsigned depmask[T];
-            depmask[0] = 0;
-#pragma unroll
-            for (int gg = 1; gg < T; ++gg) {
-                const int ig = __shfl_sync(FULL, i, gg * GL);
-                const double bx = shfl_d(ncx, gg * GL), by = shfl_d(ncy, gg * GL), bz = shfl_d(ncz, gg * GL);
-                const double ox = com[ig], oy = com[Np + ig], oz = com[2 * Np + ig];
-                bool dep = false;
-                if (grp < gg) {   // my step is the earlier one: would its move (if accepted) change what step gg saw?
-                    dep = i == ig || ((touch0[(size_t)gg * g.spec_group_doubles * 2 + (i >> 5)] >> (i & 31)) & 1u);
-                    dep = dep || !(pair_r2(ncx - bx, ncy - by, ncz - bz, g) > g.cut2);
-                    dep = dep || !(pair_r2(ox - ncx, oy - ncy, oz - ncz, g) > g.cut2);
-                }
-                const unsigned b = __ballot_sync(FULL, dep);
-                unsigned dm = 0;
-#pragma unroll
-                for (int g2 = 0; g2 < T; ++g2) dm |= ((b >> (g2 * GL)) & 1u) << g2;
-                depmask[gg] = dm;
+            bool dep = false;
+            if (gb < T) {   // would the move of step ga, if accepted, change what step gb saw?
+                const SpecX xa = xch[ga], xb = xch[gb];
+                const unsigned *tb = reinterpret_cast<const unsigned *>(wk0 + (size_t)gb * g.spec_group_doubles + g.o_touch);
+                dep = xa.i == xb.i || ((tb[xa.i >> 5] >> (xa.i & 31)) & 1u);
+                dep = dep || !(pair_r2(xa.ncx - xb.ncx, xa.ncy - xb.ncy, xa.ncz - xb.ncz, g) > g.cut2);
+                dep = dep || !(pair_r2(com[xb.i] - xa.ncx, com[Np + xb.i] - xa.ncy, com[2 * Np + xb.i] - xa.ncz, g) > g.cut2);
             }
+            const unsigned depbits = __ballot_sync(FULL, dep);
+            unsigned acc_valid = xch[0].flags & 1u;
 #pragma unroll
             for (int gg = 1; gg < T; ++gg) {
-                if (progress == gg && gg < limit && (depmask[gg] & acc_valid) == 0) {
+                const unsigned dm = (depbits >> (gg * (gg - 1) / 2)) & ((1u << gg) - 1u);
+                if (progress == gg && gg < limit && (dm & acc_valid) == 0) {
                     progress = gg + 1;
-                    acc_valid |= ((accmask >> (gg * GL)) & 1u) << gg;
+                    acc_valid |= (unsigned)(xch[gg].flags & 1) << gg;
                 }
             }
         }
-        (void)limit;
         // ================= commit the accepted steps that stand (they are mutually independent) =================
-        const bool mine = grp < progress && accept;
-        if (mine) {
-            for (int c0 = 0; c0 < N; c0 += 32)
+        if (gidx < progress && accept) {
+            // entries of partners that left the cutoff go to zero; partners inside it are overwritten below
+            if (N <= 32) {
+                const unsigned gone = oldw0 & ~neww0;
 #pragma unroll
                 for (int m = 0; m < MCH; ++m) {
-                    const int j = c0 + r + GL * m;
-                    if (j < N && (MAT_SMEM || mat[(size_t)i * MS + j] != 0.0)) { mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0; }
+                    const int j = r + GL * m;
+                    if ((gone >> j) & 1u) { mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0; }
                 }
+            } else {
+                for (int c0 = 0, w = 0; c0 < N; c0 += 32, ++w)
+#pragma unroll
+                    for (int m = 0; m < MCH; ++m) {
+                        const int j = c0 + r + GL * m;
+                        if (j < N && mat[(size_t)i * MS + j] != 0.0) { mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0; }
+                    }
+            }
             if (r >= 1 && r <= 6) base[i] = nv;
             if (r < 4) {
                 sites[SITE_DOUBLES * i + 3 * a] = sx; sites[SITE_DOUBLES * i + 3 * a + 1] = sy;
                 sites[SITE_DOUBLES * i + 3 * a + 2] = sz;
             }
-            if (r == 0) {
-                double es = 0.0;
-                for (int p = 0; p < nsolp; ++p) es += (epart[4 * p] + epart[4 * p + 1]) + (epart[4 * p + 2] + epart[4 * p + 3]);
-                energy[i] = es;
-            }
+            if (r == 0) energy[i] = esol;
         }
-        __syncwarp();
-        if (mine) {
-            for (int sl = nsolp + r; sl < nslots; sl += GL) {
+        if (N > 32) __syncwarp();
+        if (gidx < progress && accept) {
+            for (int sl = nsolp + r; sl < nslots; sl += GL) {        // SS(i,j) = SS(j,i) = EN, :819-820
                 const int j = list[sl];
                 const double e = (epart[4 * sl] + epart[4 * sl + 1]) + (epart[4 * sl + 2] + epart[4 * sl + 3]);
                 mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
             }
         }
-        // ================= bookkeeping in step order =================
+        // ================= bookkeeping in step order (every warp keeps the same copy) =================
 #pragma unroll
         for (int gg = 0; gg < T; ++gg) {
-            const double dEg = shfl_d(dE, gg * GL);
-            const int nng = __shfl_sync(FULL, nn, gg * GL);
             if (gg < progress) {
-                const bool accg = (accmask >> (gg * GL)) & 1u;
-                uused += 7 + ((u8mask >> (gg * GL)) & 1u);
-                nclamp += (clmask >> (gg * GL)) & 1u;
-                sitepairs += (unsigned)(wpair * nng + wsol);
-                s.last_delta = dEg;
+                const SpecX x = xch[gg];
+                uused += 7 + ((x.flags >> 1) & 1);
+                nclamp += (x.flags >> 2) & 1;
+                sitepairs += (unsigned)(wpair * x.nn + wsol);
+                s.last_delta = x.dE;
                 const bool in_prod = (long long)(step0 + (unsigned)(done + gg) + 1ULL) >= s.start_prod;
-                if (accg) {
+                if (x.flags & 1) {
                     nsuc++; nacc++;
-                    s.toteng += dEg;
+                    s.toteng += x.dE;
                     if (in_prod) { s.production += s.toteng; prod_acc++; }
                 }
                 if (in_prod) { s.sum_e += s.toteng; s.sum_e2 = fma(s.toteng, s.toteng, s.sum_e2); nstat++; }
@@ -712,18 +723,18 @@ __global__ void __launch_bounds__(32) k_run_spec(Geo g, SiteRel rel, double *ima
             nacc = 0;
         }
         done += progress;
-        __syncwarp();
+        if (W > 1) __syncthreads(); else __syncwarp();
         PH_T(4);
     }
 #ifdef MCB_PHASE_CLOCKS
-    if (lane == 0) for (int qq = 0; qq < 8; ++qq) atomicAdd(&g_phase[qq], (unsigned long long)ph[qq]);
+    if (tid == 0) for (int qq = 0; qq < 8; ++qq) atomicAdd(&g_phase[qq], (unsigned long long)ph[qq]);
 #endif
     {
         const int n_mut = g.o_sites + SITE_DOUBLES * N;
-        for (int qq = lane; qq < n_mut; qq += 32) gimg[qq] = img[qq];
-        if (MAT_SMEM) for (int qq = lane; qq < N * MS; qq += 32) gimg[g.o_mat + qq] = img[g.o_mat + qq];
+        for (int qq = tid; qq < n_mut; qq += 32 * W) gimg[qq] = img[qq];
+        if (MAT_SMEM) for (int qq = tid; qq < N * MS; qq += 32 * W) gimg[g.o_mat + qq] = img[g.o_mat + qq];
     }
-    if (lane == 0) {
+    if (tid == 0) {
         s.step += done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.uused += uused; s.prod_acc += prod_acc;
         s.nstat += nstat; s.sitepairs += (long long)sitepairs;
         if (done > 0) s.ratio = (double)((float)racc / (float)s.nadj);

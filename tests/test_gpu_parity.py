@@ -212,7 +212,7 @@ def test_batched_mode_with_driver_uniforms(shipped):
         _compare_chain(st, c, o.stats(), com, hoek, o)
 
 
-@pytest.mark.parametrize("lookahead", [1, 2, 4])
+@pytest.mark.parametrize("lookahead", [1, 2, 4, 8])
 def test_batched_mode_builtin_stream_and_resume(shipped, lookahead):
     """Built-in counter stream, run in three launches (resume across launches must be seamless), for every
     speculative look-ahead depth: the chain must be the sequential one, decision for decision."""

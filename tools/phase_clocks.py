@@ -32,4 +32,5 @@ names = ["mcinit (rng, old row, move, sincos, rotate)", "centre-of-mass gate + l
 tot = sum(buf[:5])
 for n, v in zip(names, buf[:5]):
     print(f"{n:32s} {v / (nch * S):9.1f} cyc/step  {100.0 * v / tot:5.1f}%")
-print(f"{'total':32s} {tot / (nch * S):9.1f} cyc/step (per committed step, lookahead={la})")
+import os
+print(f"{'total':32s} {tot / (nch * S):9.1f} cyc/step (per committed step, lookahead={la}, tune={os.environ.get('MCB200_TUNE')})")
