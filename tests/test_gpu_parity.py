@@ -294,6 +294,36 @@ def test_per_chain_solute_conformers(shipped):
     assert len(set(np.round(tot, 6))) == nch
 
 
+def test_config4_dihedral_sweep(shipped):
+    """BASELINE config 4 in miniature: 36 solute conformers (dihedral 9-8-1-2 set to 0..350 degrees by the host-side
+    generator) x 3 chains each; every chain must be the oracle's chain for its own conformer, and the per-angle
+    statistics are what the end-of-run gather collects."""
+    from montecarlo_b200 import dihedral
+    box, system = shipped
+    conf, atoms = dihedral.conformer_sweep(box.solute, box.sol_sym, box.dihedrals[0][:2], np.arange(0.0, 360.0, 10.0))
+    per = 3
+    nch = conf.shape[0] * per
+    sol = np.repeat(conf, per, axis=0)
+    eng = _engine(system, box.n, n_chains=nch)
+    eng.set_solute(sol, np.broadcast_to(system.sol_tab, (nch,) + system.sol_tab.shape).copy())
+    eng.set_state(box.com, box.hoek)
+    tot0 = eng.total_energy()[0]
+    seeds = np.arange(1, nch + 1, dtype=np.uint64)
+    eng.seed(seeds)
+    eng.run_steps(1000)
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    for c in (0, 1, 50, nch - 1):
+        o = ol.OracleChain(system, box.com, box.hoek, solute=sol[c])
+        assert abs(o.total_energy() - tot0[c]) <= RTOL * abs(tot0[c])
+        o.run_steps_rng(1000, ol.rng_seed(int(seeds[c])), trace=False)
+        _compare_chain(st, c, o.stats(), com, hoek, o)
+    e0 = tot0.reshape(-1, per)
+    assert np.all(e0 == e0[:, :1]) and len(np.unique(np.round(e0[:, 0], 6))) == 36   # same conformer, same start energy
+    per_angle_mean = (st["sum_e"] / st["n_stat"]).reshape(-1, per).mean(axis=1)
+    assert per_angle_mean.shape == (36,) and np.all(np.isfinite(per_angle_mean))
+
+
 def test_quirk_31_and_odd_sizes(shipped):
     """N = 33 random box: molecule 31 is never picked, 30 twice as often (MonteCarlo.F90:698); N not a multiple of 4."""
     box, system = shipped
