@@ -110,7 +110,7 @@ static void setup_geo(mcb_handle *h)
     }
     if (const char *t = getenv("MCB200_TUNE")) {
         int w = 0, gl = 0;
-        if (sscanf(t, "%d,%d", &w, &gl) == 2 && (w == 1 || w == 2 || w == 4) && (gl == 8 || gl == 16 || gl == 32) && w * 32 / gl <= 8) {
+        if (sscanf(t, "%d,%d", &w, &gl) == 2 && ((w == 1 && (gl == 8 || gl == 16 || gl == 32)) || (w == 2 && (gl == 8 || gl == 16)))) {
             h->spec_w = w; h->spec_gl = gl; h->lookahead = w * 32 / gl;
         }
     }
@@ -229,10 +229,12 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
         int rc = 0;
         rc |= set_smem_attr(h, k_run_steps<false, true, false>, h->smem_bytes); rc |= set_smem_attr(h, k_run_steps<false, true, true>, h->smem_bytes);
         rc |= set_smem_attr(h, k_run_steps<true, true, false>, h->smem_bytes);  rc |= set_smem_attr(h, k_run_steps<true, true, true>, h->smem_bytes);
-#define SPEC_ATTR(GL, W) rc |= set_smem_attr(h, k_run_spec<false, false, GL, W>, h->smem_spec_bytes); rc |= set_smem_attr(h, k_run_spec<false, true, GL, W>, h->smem_spec_bytes); \
-                         rc |= set_smem_attr(h, k_run_spec<true, false, GL, W>, h->smem_spec_bytes);  rc |= set_smem_attr(h, k_run_spec<true, true, GL, W>, h->smem_spec_bytes);
-        SPEC_ATTR(32, 1) SPEC_ATTR(32, 2) SPEC_ATTR(32, 4) SPEC_ATTR(16, 1) SPEC_ATTR(16, 2) SPEC_ATTR(16, 4) SPEC_ATTR(8, 1) SPEC_ATTR(8, 2)
+#define SPEC_ATTR1(GL, W, S) rc |= set_smem_attr(h, k_run_spec<false, false, GL, W, S>, h->smem_spec_bytes); rc |= set_smem_attr(h, k_run_spec<false, true, GL, W, S>, h->smem_spec_bytes); \
+                            rc |= set_smem_attr(h, k_run_spec<true, false, GL, W, S>, h->smem_spec_bytes);  rc |= set_smem_attr(h, k_run_spec<true, true, GL, W, S>, h->smem_spec_bytes);
+#define SPEC_ATTR(GL, W) SPEC_ATTR1(GL, W, true) SPEC_ATTR1(GL, W, false)
+        SPEC_ATTR(32, 1) SPEC_ATTR(16, 1) SPEC_ATTR(8, 1) SPEC_ATTR(16, 2) SPEC_ATTR(8, 2)
 #undef SPEC_ATTR
+#undef SPEC_ATTR1
         if (rc) return fail(rc);
     }
 #undef CKC
@@ -578,13 +580,19 @@ static void launch_run_ubuf(mcb_t *h, long long nsteps, long long cap, long long
         k_run_steps<COUL, true, false><<<h->n_chains, 32, h->smem_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, h->d_ubuf, cap, d_consumed, d_steps);
 }
 
+template <bool COUL, int GL, int W, bool SMALL>
+static void launch_run_spec2(mcb_t *h, long long nsteps, long long *d_steps)
+{
+    if (h->g.mat_in_image)
+        k_run_spec<COUL, true, GL, W, SMALL><<<h->n_chains, 32 * W, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps);
+    else
+        k_run_spec<COUL, false, GL, W, SMALL><<<h->n_chains, 32 * W, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps);
+}
+
 template <bool COUL, int GL, int W>
 static void launch_run_spec(mcb_t *h, long long nsteps, long long *d_steps)
 {
-    if (h->g.mat_in_image)
-        k_run_spec<COUL, true, GL, W><<<h->n_chains, 32 * W, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps);
-    else
-        k_run_spec<COUL, false, GL, W><<<h->n_chains, 32 * W, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps);
+    if (h->g.N <= 32) launch_run_spec2<COUL, GL, W, true>(h, nsteps, d_steps); else launch_run_spec2<COUL, GL, W, false>(h, nsteps, d_steps);
 }
 
 template <bool COUL>
@@ -593,11 +601,8 @@ static void launch_run_spec_any(mcb_t *h, long long nsteps, long long *d_steps)
     const int key = h->spec_gl * 10 + h->spec_w;
     switch (key) {
         case 321: launch_run_spec<COUL, 32, 1>(h, nsteps, d_steps); break;
-        case 322: launch_run_spec<COUL, 32, 2>(h, nsteps, d_steps); break;
-        case 324: launch_run_spec<COUL, 32, 4>(h, nsteps, d_steps); break;
         case 161: launch_run_spec<COUL, 16, 1>(h, nsteps, d_steps); break;
         case 162: launch_run_spec<COUL, 16, 2>(h, nsteps, d_steps); break;
-        case 164: launch_run_spec<COUL, 16, 4>(h, nsteps, d_steps); break;
         case 81: launch_run_spec<COUL, 8, 1>(h, nsteps, d_steps); break;
         default: launch_run_spec<COUL, 8, 2>(h, nsteps, d_steps); break;
     }

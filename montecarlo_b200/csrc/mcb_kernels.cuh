@@ -482,7 +482,7 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
 struct SpecX { double dE, esol, ncx, ncy, ncz; int i, nn, flags, pad; };   // what a step hands to the resolution
 constexpr int SPECX_DOUBLES = sizeof(SpecX) / 8;
 
-template <bool COUL, bool MAT_SMEM, int GL, int W>
+template <bool COUL, bool MAT_SMEM, int GL, int W, bool SMALL>
 __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl,
                                                      long long nsteps, long long *out_steps)
 {
@@ -493,10 +493,12 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
     constexpr unsigned GMASK = GL == 32 ? 0xffffffffu : ((1u << GL) - 1u);
     static_assert(GL == 8 || GL == 16 || GL == 32, "a step needs 7 role lanes");
     static_assert(T <= 8, "the resolution handles at most 8 steps (28 ordered pairs, one per lane)");
+    // SMALL: N <= 32, i.e. one 32-molecule chunk: the chunk loops below unroll into straight-line code
     extern __shared__ __align__(16) double smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int c = blockIdx.x;
     const int N = g.N, Np = g.Np, MS = g.MS, nsolp = g.nsolp;
+    const int nchunk = SMALL ? 1 : (N + 31) >> 5;
     double *gimg = images + (size_t)c * g.image_doubles;
     double *img = smem;
     {
@@ -564,7 +566,9 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
         // old row of the pair matrix + ENERGY(i); its non-zero pattern is half of the "touch" set
         double old_part = r == 0 ? energy[i] : 0.0;
         unsigned oldw0 = 0;
-        for (int c0 = 0, w = 0; c0 < N; c0 += 32, ++w) {
+#pragma unroll
+        for (int w = 0; w < nchunk; ++w) {
+            const int c0 = 32 * w;
             unsigned word = 0;
 #pragma unroll
             for (int m = 0; m < MCH; ++m) {
@@ -591,7 +595,9 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
         // centre-of-mass gate (:804-813): MCH partners per lane and chunk
         int nn = 0;
         unsigned neww0 = 0;
-        for (int c0 = 0, w = 0; c0 < N; c0 += 32, ++w) {
+#pragma unroll
+        for (int w = 0; w < nchunk; ++w) {
+            const int c0 = 32 * w;
             unsigned word = 0;
             bool in[MCH];
 #pragma unroll
@@ -664,7 +670,7 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
         // ================= commit the accepted steps that stand (they are mutually independent) =================
         if (gidx < progress && accept) {
             // entries of partners that left the cutoff go to zero; partners inside it are overwritten below
-            if (N <= 32) {
+            if (SMALL) {
                 const unsigned gone = oldw0 & ~neww0;
 #pragma unroll
                 for (int m = 0; m < MCH; ++m) {
@@ -686,7 +692,7 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
             }
             if (r == 0) energy[i] = esol;
         }
-        if (N > 32) __syncwarp();
+        if (!SMALL) __syncwarp();
         if (gidx < progress && accept) {
             for (int sl = nsolp + r; sl < nslots; sl += GL) {        // SS(i,j) = SS(j,i) = EN, :819-820
                 const int j = list[sl];
