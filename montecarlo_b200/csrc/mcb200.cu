@@ -115,7 +115,7 @@ static void setup_geo(mcb_handle *h)
         }
     }
     h->smem_bytes = ((size_t)g.stage_doubles + g.work_doubles) * 8;
-    h->smem_spec_bytes = ((size_t)g.stage_doubles + (size_t)h->lookahead * (g.work_doubles + SPECX_DOUBLES) + 2) * 8;
+    h->smem_spec_bytes = ((size_t)g.stage_doubles + (size_t)h->lookahead * (g.work_doubles + SPECX_DOUBLES) + 64 + 6 * 64 + 32 + 2) * 8;
     h->can_step = h->smem_spec_bytes <= 227 * 1024;
 }
 

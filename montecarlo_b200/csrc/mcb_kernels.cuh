@@ -519,6 +519,11 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
     double *const epart = wk + g.o_epart;
     unsigned *const touch = reinterpret_cast<unsigned *>(wk + g.o_touch);
     SpecX *const xch = reinterpret_cast<SpecX *>(wk0 + (size_t)T * g.spec_group_doubles);
+    // ring of pre-drawn trial moves: 64 entries indexed by (step & 63), refilled 32 steps at a time with one
+    // step per lane, so the uniforms, the molecule pick and log(u7) cost ~8 instructions per step instead of ~60
+    double *const ring_thr = reinterpret_cast<double *>(xch) + (size_t)T * SPECX_DOUBLES;
+    double *const ring_rv = ring_thr + 64;
+    int *const ring_i = reinterpret_cast<int *>(ring_rv + 6 * 64);
     ChainCtl s = ctl[c];
     for (int p = r; p < nsolp; p += GL) list[p] = N + p;
     __syncthreads();
@@ -538,7 +543,6 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
     double *const base = (isang ? hoek : com) + k * Np;
     const double period = isang ? TAU_D : g.boxl2, half = isang ? PI_D : g.boxl;
     const double inv_half = isang ? 1.0 / PI_D : g.inv_boxl;
-    const double f1 = isang ? 1.0 : INV_SQRT3;
     // which ordered pair (ga < gb) of steps this lane checks in the resolution
     int gb = 1;
     while (gb * (gb + 1) / 2 <= lane) ++gb;
@@ -549,20 +553,34 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
     unsigned long long sitepairs = 0;
     const unsigned long long step0 = (unsigned long long)s.step;
     const int nsteps_i = (int)min(nsteps, (long long)0x3fffffff);
+    unsigned long long gen_end = step0;                             // ring holds steps [.., gen_end)
 #ifdef MCB_PHASE_CLOCKS
     long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tph = clock64();
 #endif
 
     while (done < nsteps_i) {
+        // ================= pre-draw the next 32 steps when the ring runs low (one step per lane) =================
+        while (step0 + (unsigned)done + T > gen_end) {
+            const unsigned long long sidx = gen_end + (unsigned)lane;
+            const int e = (int)(sidx & 63ULL);
+            const double u0 = stream_uniform(s.rng_key, 8ULL * sidx);
+            int ii = (int)(u0 * (double)N) + 1;                     // MCINIT, MonteCarlo.F90:697-698
+            if (g.quirk31 && ii == 31) ii = 30;
+            ring_i[e] = min(ii, N) - 1;
+#pragma unroll
+            for (int q = 0; q < 6; ++q) {                           // randVec / randVecHoek before the step size, lib.f90:111-131
+                const double rvu = (stream_uniform(s.rng_key, 8ULL * sidx + 1 + q) - 0.5) * 2.0;
+                ring_rv[6 * e + q] = (q < 3 ? INV_SQRT3 : 1.0) * rvu;
+            }
+            // METROPOLIS draws RV <= E**x; with x < 0 that is log(RV)/log(E) <= x, and the left side needs only the uniform
+            ring_thr[e] = log(stream_uniform(s.rng_key, 8ULL * sidx + 7)) * (1.0 / LN_E_F32);
+            gen_end += 32;
+            __syncwarp();
+        }
         // ================= evaluation of step (done + gidx) by this group =================
-        const double myu = stream_uniform(s.rng_key, 8ULL * (step0 + (unsigned)(done + gidx)) + (unsigned)(r & 7));
-        const double u0 = shfl_d(myu, leader);
-        // METROPOLIS draws RV <= E**x; with x < 0 that is log(RV)/log(E) <= x.  The left side only needs the uniform,
-        // so it is ready long before dE is.
-        const double thr = shfl_d(log(myu) * (1.0 / LN_E_F32), leader + 7);
-        int i = (int)(u0 * (double)N) + 1;                          // MCINIT, MonteCarlo.F90:697-698
-        if (g.quirk31 && i == 31) i = 30;
-        i = min(i, N) - 1;
+        const int ring_e = (int)((step0 + (unsigned)(done + gidx)) & 63ULL);
+        const int i = ring_i[ring_e];
+        const double thr = ring_thr[ring_e];
         // old row of the pair matrix + ENERGY(i); its non-zero pattern is half of the "touch" set
         double old_part = r == 0 ? energy[i] : 0.0;
         unsigned oldw0 = 0;
@@ -580,9 +598,7 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
             }
             if (w == 0) oldw0 = word; else if (r == 0) touch[w] = word;
         }
-        double rv = (myu - 0.5) * 2.0;                               // randVec / randVecHoek, lib.f90:111-131
-        rv = f1 * rv;
-        rv = (isang ? s.dhoekmax : s.dposmax) * rv;
+        const double rv = (isang ? s.dhoekmax : s.dposmax) * ring_rv[6 * ring_e + rr];
         const double nv = wrap_checked(base[i] + rv, period, half, inv_half);   // :699-712
         double sn, cs;
         sincos(nv, &sn, &cs);
