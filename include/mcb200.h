@@ -42,7 +42,7 @@ typedef struct {
     int quirk_31;           /* 1 = keep `IF (RSOLV .EQ. 31) RSOLV = 30` (MonteCarlo.F90:698) in mcb_run_steps */
     int matrix_mode;        /* 0 auto, 1 force the pair matrix into global memory (never shared memory) */
     int lookahead;          /* steps of a chain evaluated speculatively at once by mcb_run_steps' built-in-stream
-                               path: 1, 2, 4 or 8; 0 = default (2).  Does not change any decision of the chain. */
+                               path: 1, 2, 4 or 8; 0 = default (1 = none).  Does not change any decision of the chain. */
     double boxl;            /* half side, Angstrom */
     double cutoff;          /* centre-of-mass cutoff, 7.0 in the reference (MonteCarlo.F90:812) */
     double conv;            /* factor on the Coulomb sum; the reference's value is exactly 0.0 (LennardJones.f90:57) */

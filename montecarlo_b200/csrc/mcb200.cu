@@ -101,12 +101,12 @@ static void setup_geo(mcb_handle *h)
     g.quirk31 = p.quirk_31;
     g.boxl = p.boxl; g.boxl2 = p.boxl * 2.0; g.inv_boxl = 1.0 / p.boxl; g.cut2 = exact_cut2(p.cutoff); g.conv = p.conv;
     // steps in flight per chain -> (warps per chain, lanes per step); MCB200_TUNE="W,GL" overrides (tuning only)
-    h->lookahead = p.lookahead == 1 || p.lookahead == 2 || p.lookahead == 4 || p.lookahead == 8 ? p.lookahead : 2;
-    switch (h->lookahead) {   // measured on configs[1] (profiles/tune_r01*.txt): sharing a warp between two steps wins
-        case 1: h->spec_w = 1; h->spec_gl = 32; break;
+    h->lookahead = p.lookahead == 1 || p.lookahead == 2 || p.lookahead == 4 || p.lookahead == 8 ? p.lookahead : 1;
+    switch (h->lookahead) {   // measured on configs[1] (profiles/tune_r01*.txt): once the scalar part of a step was made cheap, no look-ahead wins
         case 4: h->spec_w = 1; h->spec_gl = 8; break;
         case 8: h->spec_w = 2; h->spec_gl = 8; break;
-        default: h->spec_w = 1; h->spec_gl = 16; break;
+        case 2: h->spec_w = 1; h->spec_gl = 16; break;
+        default: h->spec_w = 1; h->spec_gl = 32; break;
     }
     if (const char *t = getenv("MCB200_TUNE")) {
         int w = 0, gl = 0;

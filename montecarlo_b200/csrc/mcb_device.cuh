@@ -145,6 +145,41 @@ __device__ __forceinline__ void rotate_site(double c1, double s1, double c2, dou
     oz = cz + (m31 * rx + m32 * ry + m33 * rz);
 }
 
+// sin and cos of an angle in [-2 pi, 2 pi] (the wrapped Euler angles, MonteCarlo.F90:705-707), for RotMatrix
+// (lib.f90:52-57).  Cody-Waite reduction to |r| <= pi/4 with pi/2 in two parts under FMA, then the fdlibm
+// kernel polynomials (error < 1 ulp), coefficients in constant memory so that the DFMAs read them as c[][]
+// operands.  The library sincos() costs ~50 warp instructions here, 16 of them UMOVs that only materialise
+// coefficients; this one ~30.
+__constant__ double SINCOS_C[16] = {
+    -1.66666666666666324348e-01, 8.33333333332248946124e-03, -1.98412698298579493134e-04,     // S1..S6
+    2.75573137070700676789e-06, -2.50507602534068634195e-08, 1.58969099521155010221e-10,
+    4.16666666666666019037e-02, -1.38888888888741095749e-03, 2.48015872894767294178e-05,      // C1..C6
+    -2.75573143513906633035e-07, 2.08757232129817482790e-09, -1.13596475577881948265e-11,
+    6.36619772367581382433e-01,   // 2/pi
+    1.57079632679489655800e+00,   // pi/2 high
+    6.12323399573676603587e-17,   // pi/2 low
+    6755399441055744.0};          // 1.5 * 2^52
+__device__ __forceinline__ void sincos_small(double x, double &sn, double &cs)
+{
+    const double t = fma(x, SINCOS_C[12], SINCOS_C[15]);
+    const int k = __double2loint(t);
+    const double kd = t - SINCOS_C[15];
+    double r = fma(-kd, SINCOS_C[13], x);
+    r = fma(-kd, SINCOS_C[14], r);
+    const double z = r * r;
+    double ps = fma(z, SINCOS_C[5], SINCOS_C[4]);
+    double pc = fma(z, SINCOS_C[11], SINCOS_C[10]);
+    ps = fma(z, ps, SINCOS_C[3]); pc = fma(z, pc, SINCOS_C[9]);
+    ps = fma(z, ps, SINCOS_C[2]); pc = fma(z, pc, SINCOS_C[8]);
+    ps = fma(z, ps, SINCOS_C[1]); pc = fma(z, pc, SINCOS_C[7]);
+    ps = fma(z, ps, SINCOS_C[0]); pc = fma(z, pc, SINCOS_C[6]);
+    const double s0 = fma(z * r, ps, r);                    // r + r^3 * S(z)
+    const double c0 = fma(z * z, pc, fma(z, -0.5, 1.0));    // 1 - z/2 + z^2 * C(z)
+    const double ss = (k & 1) ? c0 : s0, cc = (k & 1) ? s0 : c0;
+    sn = (k & 2) ? -ss : ss;
+    cs = ((k + 1) & 2) ? -cc : cc;
+}
+
 // Uniform stream (include/mcb200.h, mcb_seed_chains): u_n = (mix(key + (n+1) G) >> 11) * 2^-53, random access
 // in n; Metropolis step s (0-based) of a chain owns n = 8 s .. 8 s + 7.
 __device__ __forceinline__ unsigned long long mix64(unsigned long long x)

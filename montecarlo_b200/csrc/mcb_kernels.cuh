@@ -596,12 +596,12 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
                 const unsigned b = __ballot_sync(FULL, v != 0.0);
                 word |= ((b >> leader) & GMASK) << (GL * m);
             }
-            if (w == 0) oldw0 = word; else if (r == 0) touch[w] = word;
+            if (w == 0) oldw0 = word; else if (T > 1 && r == 0) touch[w] = word;
         }
         const double rv = (isang ? s.dhoekmax : s.dposmax) * ring_rv[6 * ring_e + rr];
         const double nv = wrap_checked(base[i] + rv, period, half, inv_half);   // :699-712
         double sn, cs;
-        sincos(nv, &sn, &cs);
+        sincos_small(nv, sn, cs);
         const double ncx = shfl_d(nv, leader + 1), ncy = shfl_d(nv, leader + 2), ncz = shfl_d(nv, leader + 3);
         const double c1 = shfl_d(cs, leader + 4), s1 = shfl_d(sn, leader + 4), c2 = shfl_d(cs, leader + 5),
                      s2 = shfl_d(sn, leader + 5), c3 = shfl_d(cs, leader + 6), s3 = shfl_d(sn, leader + 6);
@@ -627,8 +627,8 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
 #pragma unroll
             for (int m = 0; m < MCH; ++m)
                 if (in[m]) list[nsolp + nn + __popc(word & ((1u << (r + GL * m)) - 1u))] = c0 + r + GL * m;
-            if (w == 0) { neww0 = word; if (r == 0) touch[0] = oldw0 | word; }
-            else if (r == 0) touch[w] |= word;
+            if (w == 0) { neww0 = word; if (T > 1 && r == 0) touch[0] = oldw0 | word; }
+            else if (T > 1 && r == 0) touch[w] |= word;
             nn += __popc(word);
         }
         __syncwarp();
@@ -652,14 +652,14 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
         const bool clamped = !(fabs(dE) <= DBL_HUGE);                // Inf/NaN trial energy: clamped, rejected (:421-428)
         const bool used8 = !clamped && exponent >= -75.0 && exponent < 0.0;
         const bool accept = !clamped && (exponent >= 0.0 || (used8 && thr <= exponent));
-        if (r == 0) {
+        if (T > 1 && r == 0) {
             SpecX x;
             x.dE = dE; x.esol = esol; x.ncx = ncx; x.ncy = ncy; x.ncz = ncz; x.i = i; x.nn = nn;
             x.flags = (accept ? 1 : 0) | (used8 ? 2 : 0) | (clamped ? 4 : 0); x.pad = 0;
             xch[gidx] = x;
         }
         PH_T(3);
-        if (W > 1) __syncthreads(); else __syncwarp();
+        if (W > 1) __syncthreads(); else if (T > 1) __syncwarp();
         // ================= resolution (every warp, redundantly): which steps of the batch stand =================
         const int limit = min(min(T, nsteps_i - done), s.nadj - adj_count);   // a batch never runs past an adaptation
         int progress = 1;
@@ -720,7 +720,9 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
 #pragma unroll
         for (int gg = 0; gg < T; ++gg) {
             if (gg < progress) {
-                const SpecX x = xch[gg];
+                SpecX x;
+                if (T > 1) x = xch[gg];
+                else { x.dE = dE; x.nn = nn; x.flags = (accept ? 1 : 0) | (used8 ? 2 : 0) | (clamped ? 4 : 0); }   // one step in flight: no exchange
                 uused += 7 + ((x.flags >> 1) & 1);
                 nclamp += (x.flags >> 2) & 1;
                 sitepairs += (unsigned)(wpair * x.nn + wsol);
