@@ -191,7 +191,7 @@ __device__ __forceinline__ double item_energy(const Geo &g, const double *sites,
 // all r^2, all reciprocals, ...) so that one warp keeps 4*NI independent fp64 chains in flight: a lone warp gets
 // 126 cycles per site pair with the pairs written one after the other, 87 with 8 and 63 with 16 staged
 // (profiles/pairbench_r01b.txt), and with ~1.75 warps per SM sub-partition that is what decides the step time.
-// Items past the end are computed on a valid slot and dropped.
+// Items past the end are computed on slot 0 and dropped.
 template <bool COUL, int NI>
 __device__ __forceinline__ double items_staged(const Geo &g, const double *sites, const double *tabAB, const double *tabQ,
                                                const int *list, int nsolp, int nslots, int s0, int stride, int a,
@@ -206,7 +206,7 @@ __device__ __forceinline__ double items_staged(const Geo &g, const double *sites
     for (int n = 0; n < NI; ++n) {
         const int sl = s0 + n * stride;
         valid[n] = sl < nslots;
-        slot[n] = valid[n] ? sl : s0;
+        slot[n] = valid[n] ? sl : 0;   // slot 0 exists whenever a pass runs
         const double2 *sp = reinterpret_cast<const double2 *>(sites + SITE_DOUBLES * list[slot[n]]);
         const double2 v0 = sp[0], v1 = sp[1], v2 = sp[2], v3 = sp[3], v4 = sp[4], v5 = sp[5];
         // R = mol2(J) - mol1(I) (LennardJones.f90:69); only |R| is needed
