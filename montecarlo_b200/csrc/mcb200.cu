@@ -110,12 +110,12 @@ static void setup_geo(mcb_handle *h)
     }
     if (const char *t = getenv("MCB200_TUNE")) {
         int w = 0, gl = 0;
-        if (sscanf(t, "%d,%d", &w, &gl) == 2 && ((w == 1 && (gl == 8 || gl == 16 || gl == 32)) || (w == 2 && (gl == 8 || gl == 16)))) {
+        if (sscanf(t, "%d,%d", &w, &gl) == 2 && ((w == 1 && (gl == 8 || gl == 16 || gl == 32)) || (w == 2 && (gl == 8 || gl == 16 || gl == 32)) || (w == 4 && gl == 32))) {
             h->spec_w = w; h->spec_gl = gl; h->lookahead = w * 32 / gl;
         }
     }
     h->smem_bytes = ((size_t)g.stage_doubles + g.work_doubles) * 8;
-    h->smem_spec_bytes = ((size_t)g.stage_doubles + (size_t)h->lookahead * (g.work_doubles + SPECX_DOUBLES) + 64 + 6 * 64 + 32 + 2) * 8;
+    h->smem_spec_bytes = ((size_t)g.stage_doubles + (size_t)h->lookahead * (g.work_doubles + SPECX_DOUBLES) + 64 + 6 * 64 + 32 + g.Np + 2) * 8;
     h->can_step = h->smem_spec_bytes <= 227 * 1024;
 }
 
@@ -232,7 +232,7 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
 #define SPEC_ATTR1(GL, W, S) rc |= set_smem_attr(h, k_run_spec<false, false, GL, W, S>, h->smem_spec_bytes); rc |= set_smem_attr(h, k_run_spec<false, true, GL, W, S>, h->smem_spec_bytes); \
                             rc |= set_smem_attr(h, k_run_spec<true, false, GL, W, S>, h->smem_spec_bytes);  rc |= set_smem_attr(h, k_run_spec<true, true, GL, W, S>, h->smem_spec_bytes);
 #define SPEC_ATTR(GL, W) SPEC_ATTR1(GL, W, true) SPEC_ATTR1(GL, W, false)
-        SPEC_ATTR(32, 1) SPEC_ATTR(16, 1) SPEC_ATTR(8, 1) SPEC_ATTR(16, 2) SPEC_ATTR(8, 2)
+        SPEC_ATTR(32, 1) SPEC_ATTR(16, 1) SPEC_ATTR(8, 1) SPEC_ATTR(16, 2) SPEC_ATTR(8, 2) SPEC_ATTR(32, 2) SPEC_ATTR(32, 4)
 #undef SPEC_ATTR
 #undef SPEC_ATTR1
         if (rc) return fail(rc);
@@ -601,6 +601,8 @@ static void launch_run_spec_any(mcb_t *h, long long nsteps, long long *d_steps)
     const int key = h->spec_gl * 10 + h->spec_w;
     switch (key) {
         case 321: launch_run_spec<COUL, 32, 1>(h, nsteps, d_steps); break;
+        case 322: launch_run_spec<COUL, 32, 2>(h, nsteps, d_steps); break;
+        case 324: launch_run_spec<COUL, 32, 4>(h, nsteps, d_steps); break;
         case 161: launch_run_spec<COUL, 16, 1>(h, nsteps, d_steps); break;
         case 162: launch_run_spec<COUL, 16, 2>(h, nsteps, d_steps); break;
         case 81: launch_run_spec<COUL, 8, 1>(h, nsteps, d_steps); break;

@@ -524,14 +524,28 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
     double *const ring_thr = reinterpret_cast<double *>(xch) + (size_t)T * SPECX_DOUBLES;
     double *const ring_rv = ring_thr + 64;
     int *const ring_i = reinterpret_cast<int *>(ring_rv + 6 * 64);
+    // rowsum[j] = sum_i SS(i,j): what dE needs from the pair matrix.  Kept current on every accepted move, so the
+    // evaluation of a step never reads a matrix row (for large boxes that row lives in global memory).
+    double *const rowsum = ring_rv + 6 * 64 + 32;
     ChainCtl s = ctl[c];
     for (int p = r; p < nsolp; p += GL) list[p] = N + p;
     __syncthreads();
+    // column sums (= row sums, the matrix is symmetric; consecutive lanes read consecutive addresses), then TOTENG
+    // re-anchored on them so that rounding of the running sums cannot accumulate across launches
+    for (int j = tid; j < N; j += 32 * W) {
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+        int i = 0;
+        for (; i + 3 < N; i += 4) {
+            a0 += mat[(size_t)i * MS + j]; a1 += mat[(size_t)(i + 1) * MS + j];
+            a2 += mat[(size_t)(i + 2) * MS + j]; a3 += mat[(size_t)(i + 3) * MS + j];
+        }
+        for (; i < N; ++i) a0 += mat[(size_t)i * MS + j];
+        rowsum[j] = (a0 + a1) + (a2 + a3);
+    }
+    __syncthreads();
     {
         double acc = 0.0;
-        for (int i = 0; i < N; ++i)
-            for (int j = i + 1 + lane; j < N; j += 32) acc += mat[(size_t)i * MS + j];
-        for (int i = lane; i < N; i += 32) acc += energy[i];
+        for (int i = lane; i < N; i += 32) acc += fma(0.5, rowsum[i], energy[i]);
         s.toteng = warp_sum(acc);
     }
     const double relx = rel.r[3 * a], rely = rel.r[3 * a + 1], relz = rel.r[3 * a + 2];
@@ -581,23 +595,9 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
         const int ring_e = (int)((step0 + (unsigned)(done + gidx)) & 63ULL);
         const int i = ring_i[ring_e];
         const double thr = ring_thr[ring_e];
-        // old row of the pair matrix + ENERGY(i); its non-zero pattern is half of the "touch" set
-        double old_part = r == 0 ? energy[i] : 0.0;
-        unsigned oldw0 = 0;
-#pragma unroll
-        for (int w = 0; w < nchunk; ++w) {
-            const int c0 = 32 * w;
-            unsigned word = 0;
-#pragma unroll
-            for (int m = 0; m < MCH; ++m) {
-                const int j = c0 + r + GL * m;
-                const double v = j < N ? mat[(size_t)i * MS + j] : 0.0;
-                old_part += v;
-                const unsigned b = __ballot_sync(FULL, v != 0.0);
-                word |= ((b >> leader) & GMASK) << (GL * m);
-            }
-            if (w == 0) oldw0 = word; else if (T > 1 && r == 0) touch[w] = word;
-        }
+        // sum of the old matrix row + ENERGY(i), straight from the running row sums
+        const double old_tot = rowsum[i] + energy[i];
+        const double old_part = r == 0 ? old_tot : 0.0;
         const double rv = (isang ? s.dhoekmax : s.dposmax) * ring_rv[6 * ring_e + rr];
         const double nv = wrap_checked(base[i] + rv, period, half, inv_half);   // :699-712
         double sn, cs;
@@ -627,8 +627,8 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
 #pragma unroll
             for (int m = 0; m < MCH; ++m)
                 if (in[m]) list[nsolp + nn + __popc(word & ((1u << (r + GL * m)) - 1u))] = c0 + r + GL * m;
-            if (w == 0) { neww0 = word; if (T > 1 && r == 0) touch[0] = oldw0 | word; }
-            else if (T > 1 && r == 0) touch[w] |= word;
+            if (w == 0) neww0 = word;
+            if ((T > 1 || !SMALL) && r == 0) touch[w] = word;     // the partners this step looked at (resolution, commit)
             nn += __popc(word);
         }
         __syncwarp();
@@ -671,6 +671,8 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
                 dep = xa.i == xb.i || ((tb[xa.i >> 5] >> (xa.i & 31)) & 1u);
                 dep = dep || !(pair_r2(xa.ncx - xb.ncx, xa.ncy - xb.ncy, xa.ncz - xb.ncz, g) > g.cut2);
                 dep = dep || !(pair_r2(com[xb.i] - xa.ncx, com[Np + xb.i] - xa.ncy, com[2 * Np + xb.i] - xa.ncz, g) > g.cut2);
+                // a non-zero entry of step gb's old matrix row = the two molecules are inside the cutoff as committed
+                dep = dep || !(pair_r2(com[xb.i] - com[xa.i], com[Np + xb.i] - com[Np + xa.i], com[2 * Np + xb.i] - com[2 * Np + xa.i], g) > g.cut2);
             }
             const unsigned depbits = __ballot_sync(FULL, dep);
             unsigned acc_valid = xch[0].flags & 1u;
@@ -683,38 +685,52 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
                 }
             }
         }
-        // ================= commit the accepted steps that stand (they are mutually independent) =================
-        if (gidx < progress && accept) {
-            // entries of partners that left the cutoff go to zero; partners inside it are overwritten below
-            if (SMALL) {
-                const unsigned gone = oldw0 & ~neww0;
+        // ================= commit the accepted steps that stand =================
+        // They are mutually independent, but two of them can share a neighbour whose row sum both adjust, so with
+        // several steps in flight the commits run one after the other.
 #pragma unroll
-                for (int m = 0; m < MCH; ++m) {
-                    const int j = r + GL * m;
-                    if ((gone >> j) & 1u) { mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0; }
-                }
-            } else {
-                for (int c0 = 0, w = 0; c0 < N; c0 += 32, ++w)
+        for (int cg = 0; cg < T; ++cg) {
+            if (gidx == cg && gidx < progress && accept) {
+                // partners that left the cutoff: entry to zero, their row sums lose the old pair energy
+                for (int w0 = 0; w0 < nchunk; w0 += 4) {
+                    double ov[4 * MCH];
 #pragma unroll
-                    for (int m = 0; m < MCH; ++m) {
-                        const int j = c0 + r + GL * m;
-                        if (j < N && mat[(size_t)i * MS + j] != 0.0) { mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0; }
+                    for (int q = 0; q < 4; ++q)
+#pragma unroll
+                        for (int m = 0; m < MCH; ++m) {
+                            const int j = 32 * (w0 + q) + r + GL * m;
+                            ov[q * MCH + m] = (w0 + q < nchunk && j < N) ? mat[(size_t)i * MS + j] : 0.0;
+                        }
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        if (w0 + q >= nchunk) break;
+                        const unsigned neww = SMALL ? neww0 : touch[w0 + q];
+#pragma unroll
+                        for (int m = 0; m < MCH; ++m) {
+                            const int j = 32 * (w0 + q) + r + GL * m;
+                            const double old = ov[q * MCH + m];
+                            if (old != 0.0 && !((neww >> (r + GL * m)) & 1u)) {
+                                rowsum[j] -= old;
+                                mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0;
+                            }
+                        }
                     }
+                }
+                // partners inside the cutoff: SS(i,j) = SS(j,i) = EN (:819-820), row sums follow
+                for (int sl = nsolp + r; sl < nslots; sl += GL) {
+                    const int j = list[sl];
+                    const double e = (epart[4 * sl] + epart[4 * sl + 1]) + (epart[4 * sl + 2] + epart[4 * sl + 3]);
+                    rowsum[j] += e - mat[(size_t)i * MS + j];
+                    mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
+                }
+                if (r >= 1 && r <= 6) base[i] = nv;
+                if (r < 4) {
+                    sites[SITE_DOUBLES * i + 3 * a] = sx; sites[SITE_DOUBLES * i + 3 * a + 1] = sy;
+                    sites[SITE_DOUBLES * i + 3 * a + 2] = sz;
+                }
+                if (r == 0) { energy[i] = esol; rowsum[i] = (dE + old_tot) - esol; }   // new row sum = new total - ENERGY(i)
             }
-            if (r >= 1 && r <= 6) base[i] = nv;
-            if (r < 4) {
-                sites[SITE_DOUBLES * i + 3 * a] = sx; sites[SITE_DOUBLES * i + 3 * a + 1] = sy;
-                sites[SITE_DOUBLES * i + 3 * a + 2] = sz;
-            }
-            if (r == 0) energy[i] = esol;
-        }
-        if (!SMALL) __syncwarp();
-        if (gidx < progress && accept) {
-            for (int sl = nsolp + r; sl < nslots; sl += GL) {        // SS(i,j) = SS(j,i) = EN, :819-820
-                const int j = list[sl];
-                const double e = (epart[4 * sl] + epart[4 * sl + 1]) + (epart[4 * sl + 2] + epart[4 * sl + 3]);
-                mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
-            }
+            if (T > 1) { if (W > 1) __syncthreads(); else __syncwarp(); }
         }
         // ================= bookkeeping in step order (every warp keeps the same copy) =================
 #pragma unroll

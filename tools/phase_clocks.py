@@ -19,6 +19,11 @@ box = boxio.read_box(inputs / "box.txt")
 system = boxio.load_system(box, inputs / "DMSO.txt", inputs / "param.txt", inputs / "par_solute.txt")
 nch, S = int(sys.argv[1]) if len(sys.argv) > 1 else 1024, 2000
 la = int(sys.argv[2]) if len(sys.argv) > 2 else 0
+k = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+if k > 1:
+    box = boxio.replicate(box, k)
+    system = boxio.System(**{**system.__dict__, "boxl": box.boxl, "solute": box.solute})
+    S = 500
 eng = LJEngine(system, box.n, n_chains=nch, lookahead=la)
 eng.set_state(box.com, box.hoek)
 eng.seed(np.arange(1, nch + 1, dtype=np.uint64))
