@@ -598,6 +598,20 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
         // sum of the old matrix row + ENERGY(i), straight from the running row sums
         const double old_tot = rowsum[i] + energy[i];
         const double old_part = r == 0 ? old_tot : 0.0;
+        // the old matrix row itself is only needed if the move is accepted (row-sum bookkeeping); for up to 8 chunks
+        // it is fetched now so that a global-memory row has arrived by then
+        constexpr int PF = SMALL ? 1 : 8;
+        double oldrow[PF * MCH];
+        const bool prefetched = nchunk <= PF;
+        if (prefetched) {
+#pragma unroll
+            for (int q = 0; q < PF; ++q)
+#pragma unroll
+                for (int m = 0; m < MCH; ++m) {
+                    const int j = 32 * q + r + GL * m;
+                    oldrow[q * MCH + m] = (q < nchunk && j < N) ? mat[(size_t)i * MS + j] : 0.0;
+                }
+        }
         const double rv = (isang ? s.dhoekmax : s.dposmax) * ring_rv[6 * ring_e + rr];
         const double nv = wrap_checked(base[i] + rv, period, half, inv_half);   // :699-712
         double sn, cs;
@@ -608,28 +622,42 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
         double sx, sy, sz;
         rotate_site(c1, s1, c2, s2, c3, s3, relx, rely, relz, ncx, ncy, ncz, sx, sy, sz);
         PH_T(0);
-        // centre-of-mass gate (:804-813): MCH partners per lane and chunk
+        // centre-of-mass gate (:804-813): MCH partners per lane and chunk, GB chunks at a time so that their distance
+        // tests and ballots overlap instead of queueing behind one another
         int nn = 0;
         unsigned neww0 = 0;
+        constexpr int GB = SMALL ? 1 : 4;
+        for (int wb = 0; wb < nchunk; wb += GB) {
+            bool in[GB * MCH];
+            unsigned word[GB];
 #pragma unroll
-        for (int w = 0; w < nchunk; ++w) {
-            const int c0 = 32 * w;
-            unsigned word = 0;
-            bool in[MCH];
+            for (int q = 0; q < GB; ++q)
 #pragma unroll
-            for (int m = 0; m < MCH; ++m) {
-                const int j = c0 + r + GL * m;
-                in[m] = false;
-                if (j < N && j != i) in[m] = !(pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2);
-                const unsigned b = __ballot_sync(FULL, in[m]);
-                word |= ((b >> leader) & GMASK) << (GL * m);
+                for (int m = 0; m < MCH; ++m) {
+                    const int j = 32 * (wb + q) + r + GL * m;
+                    in[q * MCH + m] = false;
+                    if (j < N && j != i) in[q * MCH + m] = !(pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2);
+                }
+#pragma unroll
+            for (int q = 0; q < GB; ++q) {
+                word[q] = 0;
+#pragma unroll
+                for (int m = 0; m < MCH; ++m) {
+                    const unsigned bb = __ballot_sync(FULL, in[q * MCH + m]);
+                    word[q] |= ((bb >> leader) & GMASK) << (GL * m);
+                }
             }
 #pragma unroll
-            for (int m = 0; m < MCH; ++m)
-                if (in[m]) list[nsolp + nn + __popc(word & ((1u << (r + GL * m)) - 1u))] = c0 + r + GL * m;
-            if (w == 0) neww0 = word;
-            if ((T > 1 || !SMALL) && r == 0) touch[w] = word;     // the partners this step looked at (resolution, commit)
-            nn += __popc(word);
+            for (int q = 0; q < GB; ++q) {
+                if (wb + q < nchunk) {
+#pragma unroll
+                    for (int m = 0; m < MCH; ++m)
+                        if (in[q * MCH + m]) list[nsolp + nn + __popc(word[q] & ((1u << (r + GL * m)) - 1u))] = 32 * (wb + q) + r + GL * m;
+                    if (wb + q == 0) neww0 = word[q];
+                    if ((T > 1 || !SMALL) && r == 0) touch[wb + q] = word[q];     // the partners this step looked at (resolution, commit)
+                    nn += __popc(word[q]);
+                }
+            }
         }
         __syncwarp();
         PH_T(1);
@@ -692,23 +720,28 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
         for (int cg = 0; cg < T; ++cg) {
             if (gidx == cg && gidx < progress && accept) {
                 // partners that left the cutoff: entry to zero, their row sums lose the old pair energy
-                for (int w0 = 0; w0 < nchunk; w0 += 4) {
-                    double ov[4 * MCH];
+                if (prefetched) {
 #pragma unroll
-                    for (int q = 0; q < 4; ++q)
+                    for (int q = 0; q < PF; ++q) {
+                        if (q >= nchunk) break;
+                        const unsigned neww = SMALL ? neww0 : touch[q];
 #pragma unroll
                         for (int m = 0; m < MCH; ++m) {
-                            const int j = 32 * (w0 + q) + r + GL * m;
-                            ov[q * MCH + m] = (w0 + q < nchunk && j < N) ? mat[(size_t)i * MS + j] : 0.0;
+                            const int j = 32 * q + r + GL * m;
+                            const double old = oldrow[q * MCH + m];
+                            if (old != 0.0 && !((neww >> (r + GL * m)) & 1u)) {
+                                rowsum[j] -= old;
+                                mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0;
+                            }
                         }
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        if (w0 + q >= nchunk) break;
-                        const unsigned neww = SMALL ? neww0 : touch[w0 + q];
+                    }
+                } else {
+                    for (int w0 = 0; w0 < nchunk; ++w0) {
+                        const unsigned neww = touch[w0];
 #pragma unroll
                         for (int m = 0; m < MCH; ++m) {
-                            const int j = 32 * (w0 + q) + r + GL * m;
-                            const double old = ov[q * MCH + m];
+                            const int j = 32 * w0 + r + GL * m;
+                            const double old = j < N ? mat[(size_t)i * MS + j] : 0.0;
                             if (old != 0.0 && !((neww >> (r + GL * m)) & 1u)) {
                                 rowsum[j] -= old;
                                 mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0;
