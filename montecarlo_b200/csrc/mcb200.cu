@@ -227,8 +227,8 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
     CKC(cudaMemcpy(h->ctl, ctl.data(), nc * sizeof(ChainCtl), cudaMemcpyHostToDevice));
     if (h->can_step) {
         int rc = 0;
-        rc |= set_smem_attr(h, k_run_steps<false, true, false>, h->smem_bytes); rc |= set_smem_attr(h, k_run_steps<false, true, true>, h->smem_bytes);
-        rc |= set_smem_attr(h, k_run_steps<true, true, false>, h->smem_bytes);  rc |= set_smem_attr(h, k_run_steps<true, true, true>, h->smem_bytes);
+        rc |= set_smem_attr(h, k_run_steps<false, false>, h->smem_bytes); rc |= set_smem_attr(h, k_run_steps<false, true>, h->smem_bytes);
+        rc |= set_smem_attr(h, k_run_steps<true, false>, h->smem_bytes);  rc |= set_smem_attr(h, k_run_steps<true, true>, h->smem_bytes);
 #define SPEC_ATTR1(GL, W, S) rc |= set_smem_attr(h, k_run_spec<false, false, GL, W, S>, h->smem_spec_bytes); rc |= set_smem_attr(h, k_run_spec<false, true, GL, W, S>, h->smem_spec_bytes); \
                             rc |= set_smem_attr(h, k_run_spec<true, false, GL, W, S>, h->smem_spec_bytes);  rc |= set_smem_attr(h, k_run_spec<true, true, GL, W, S>, h->smem_spec_bytes);
 #define SPEC_ATTR(GL, W) SPEC_ATTR1(GL, W, true) SPEC_ATTR1(GL, W, false)
@@ -575,9 +575,9 @@ template <bool COUL>
 static void launch_run_ubuf(mcb_t *h, long long nsteps, long long cap, long long *d_consumed, long long *d_steps)
 {
     if (h->g.mat_in_image)
-        k_run_steps<COUL, true, true><<<h->n_chains, 32, h->smem_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, h->d_ubuf, cap, d_consumed, d_steps);
+        k_run_steps<COUL, true><<<h->n_chains, 32, h->smem_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, h->d_ubuf, cap, d_consumed, d_steps);
     else
-        k_run_steps<COUL, true, false><<<h->n_chains, 32, h->smem_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, h->d_ubuf, cap, d_consumed, d_steps);
+        k_run_steps<COUL, false><<<h->n_chains, 32, h->smem_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, h->d_ubuf, cap, d_consumed, d_steps);
 }
 
 template <bool COUL, int GL, int W, bool SMALL>

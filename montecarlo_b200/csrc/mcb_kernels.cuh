@@ -266,14 +266,13 @@ __device__ __forceinline__ double items_staged(const Geo &g, const double *sites
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Batched mode: nsteps Metropolis steps of one chain per warp, the chain's image resident in shared memory.
-//   UBUF      uniforms come from a caller buffer [chain][cap] instead of the built-in counter stream
+// Batched mode with DRIVER-SUPPLIED uniforms: nsteps Metropolis steps of one chain per warp, the chain's image
+// resident in shared memory, the uniforms read from the caller's buffer [chain][cap] in exactly the order the
+// reference draws them (7 per step, an 8th only when METROPOLIS needs it), so a buffer of the driver's RAND()
+// values reproduces the driver's accept/reject sequence.  (k_run_spec below is the fast path for the built-in
+// stream; this kernel keeps the straightforward one-step-at-a-time structure.)
 //   MAT_SMEM  the pair matrix is part of the staged image (small N); otherwise it stays in global memory
-// A chain's steps are strictly sequential and one step is only ~230 site pairs, so the kernel is shaped for
-// LATENCY: the old row is fetched as soon as the molecule is known; 16 partner slots (two per lane, eight
-// independent site pairs) are in flight at once; dE comes from a single warp reduction of per-lane partial
-// sums; the per-partner energies are parked in shared memory and only summed if the move is accepted.
-template <bool COUL, bool UBUF, bool MAT_SMEM>
+template <bool COUL, bool MAT_SMEM>
 __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl,
                                                   long long nsteps, const double *ubuf, long long cap,
                                                   long long *out_consumed, long long *out_steps)
@@ -327,20 +326,15 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
     unsigned nsuc = 0, nacc = (unsigned)s.naccept, racc = 0, nclamp = 0, uused = 0, prod_acc = 0, nstat = 0;
     unsigned long long sitepairs = 0;
     const unsigned long long step0 = (unsigned long long)s.step;
-    const double *myubuf = UBUF ? ubuf + (size_t)c * cap : nullptr;
+    const double *myubuf = ubuf + (size_t)c * cap;
     const int nsteps_i = (int)min(nsteps, (long long)0x7fffffff);
 #ifdef MCB_PHASE_CLOCKS
     long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tph = clock64();
 #endif
 
     for (; done < nsteps_i; ++done) {
-        double myu;
-        if (UBUF) {
-            if (cursor + 8 > cap) break;
-            myu = lane < 8 ? myubuf[cursor + lane] : 0.0;
-        } else {
-            myu = stream_uniform(s.rng_key, 8ULL * (step0 + (unsigned)done) + (unsigned)(lane & 7));
-        }
+        if (cursor + 8 > cap) break;
+        const double myu = lane < 8 ? myubuf[cursor + lane] : 0.0;
         // ---- MCINIT (MonteCarlo.F90:685-715): lane 0 picks the molecule, lanes 1-3 move the centre of mass,
         //      lanes 4-6 the angles (randVec / randVecHoek, lib.f90:111-131), then the wraps (:705-712)
         const double u0 = shfl_d(myu, 0);
@@ -406,7 +400,7 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
         PH_T(3);
         uused += used; s.last_delta = delta;
         sitepairs += (unsigned)(wpair * nn + wsol);
-        if (UBUF) cursor += used;
+        cursor += used;
         const bool in_prod = (long long)(step0 + (unsigned)done + 1ULL) >= s.start_prod;
         if (accept) {
             nsuc++; nacc++;
@@ -460,7 +454,7 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
         // REAL(NACCEPT)/REAL(NADJ) as METROPOLIS leaves it after its last step (:758): before the window reset
         if (done > 0) s.ratio = (double)((float)racc / (float)s.nadj);
         ctl[c] = s;
-        if (out_consumed) out_consumed[c] = UBUF ? cursor : 0;
+        if (out_consumed) out_consumed[c] = cursor;
         if (out_steps) out_steps[c] = done;
     }
 }
