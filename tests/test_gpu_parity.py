@@ -376,6 +376,31 @@ def test_edge_cases(shipped):
         eng.run_steps(5, np.zeros((1, 4)))
 
 
+def test_overlap_gives_nan_as_a_value_and_rollback_is_clean(shipped):
+    """A trial move that lands exactly on another molecule: r = 0 for the coinciding sites, the reference's
+    LJ_FORMULA gives Inf - Inf = NaN (LennardJones.f90:185) and its driver clamps and rejects (MonteCarlo.F90:421-428).
+    The single-step entry points return the NaN as a value (no clamp in the library) and a discarded trial leaves
+    the chain exactly as it was."""
+    box, system = shipped
+    eng = _engine(system, box.n, n_chains=2)
+    eng.set_state(box.com, box.hoek)
+    e0 = eng.total_energy()[0].copy()
+    d_e, e_new = eng.trial_delta([5, 5], np.stack([box.com[9], box.com[4]]), np.stack([box.hoek[9], box.hoek[4]]))
+    assert not np.isfinite(d_e[0]) and not np.isfinite(e_new[0])       # molecule 5 dropped onto molecule 10
+    assert abs(d_e[1]) <= RTOL * abs(e0[1]) and abs(e_new[1] - e0[1]) <= RTOL * abs(e0[1])   # molecule 5 "moved" onto itself
+    eng.commit([0, 1])
+    st = eng.stats()
+    assert st["toteng"][0] == e0[0] and abs(st["toteng"][1] - e0[1]) <= RTOL * abs(e0[1])
+    com, hoek = eng.get_state()
+    assert np.array_equal(com[0], box.com) and np.array_equal(com[1], box.com)
+    assert np.all(np.abs(eng.total_energy()[0] - e0) <= RTOL * np.abs(e0))
+    # the oracle sees the same thing: its trial energy is clamped to HUGE and the step is rejected
+    o = ol.OracleChain(system, box.com, box.hoek)
+    o.total_energy()
+    _, tr = o.step_given_move(4, box.com[9], box.hoek[9], 0.0)
+    assert tr[0] > 1e307 and tr[5] == 0.0 and o.stats()["nclamp"] == 1
+
+
 def test_full_size_properties(shipped):
     """BASELINE config 2 size (1024 chains of the shipped box): determinism across identical seeds, independence
     across different seeds, and running energy == fresh recompute for every chain."""
