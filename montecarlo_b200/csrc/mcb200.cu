@@ -6,6 +6,7 @@
 // that computes something launches a kernel or fails.
 #include "../../include/mcb200.h"
 #include "mcb_kernels.cuh"
+#include "mcb_verlet.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -25,6 +26,7 @@ struct mcb_handle {
     bool coul = false, can_step = false, dirty = true, energy_only = false;
     double *big_e = nullptr, *big_sol = nullptr, *big_out = nullptr; long long *big_n = nullptr, *big_nout = nullptr;
     long long big_blocks = 0; int big_tiles = 0;
+    VerletBufs vl{};        // neighbour lists of k_run_vl (large boxes); idx == nullptr: not in use
     cudaStream_t stream = nullptr;
     double *images = nullptr, *matg = nullptr, *work = nullptr;
     ChainCtl *ctl = nullptr;
@@ -99,7 +101,7 @@ static void setup_geo(mcb_handle *h)
     g.image_doubles = (int)(mat_smem ? with_mat : (size_t)end_tab);
     g.stage_doubles = g.image_doubles;
     g.quirk31 = p.quirk_31;
-    g.boxl = p.boxl; g.boxl2 = p.boxl * 2.0; g.inv_boxl = 1.0 / p.boxl; g.cut2 = exact_cut2(p.cutoff); g.conv = p.conv;
+    g.boxl = p.boxl; g.boxl2 = p.boxl * 2.0; g.inv_boxl = 1.0 / p.boxl; g.cut2 = exact_cut2(p.cutoff); g.conv = p.conv; g.cutoff = p.cutoff;
     // steps in flight per chain -> (warps per chain, lanes per step); MCB200_TUNE="W,GL" overrides (tuning only)
     h->lookahead = p.lookahead == 1 || p.lookahead == 2 || p.lookahead == 4 || p.lookahead == 8 ? p.lookahead : 1;
     switch (h->lookahead) {   // measured on configs[1] (profiles/tune_r01*.txt): once the scalar part of a step was made cheap, no look-ahead wins
@@ -128,6 +130,7 @@ extern "C" int mcb_destroy(mcb_t *h)
     cudaFree(h->images); cudaFree(h->matg); cudaFree(h->work); cudaFree(h->ctl);
     cudaFree(h->d_rsolv); cudaFree(h->d_vec); cudaFree(h->d_out); cudaFree(h->d_ll); cudaFree(h->d_acc);
     cudaFree(h->d_ubuf);
+    cudaFree(h->vl.idx); cudaFree(h->vl.cnt); cudaFree(h->vl.ref);
     cudaFree(h->big_e); cudaFree(h->big_sol); cudaFree(h->big_out); cudaFree(h->big_n); cudaFree(h->big_nout);
     if (h->pin) cudaFreeHost(h->pin);
     delete h;
@@ -202,6 +205,19 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
         CKC(cudaMalloc(&h->big_sol, sizeof(double) * h->big_tiles));
         CKC(cudaMalloc(&h->big_out, sizeof(double) * 2));
         CKC(cudaMalloc(&h->big_nout, sizeof(long long)));
+    }
+    // neighbour lists pay once the gate has more than ~8 chunks of 32 molecules to scan: at N = 240 k_run_spec's chunked
+    // gate is as fast (4.6e10 vs 4.5e10 site pairs/s), at N = 810 the lists are 3x faster (profiles/other_configs_r01.txt)
+    int vl_min_n = 257;
+    if (const char *mn = getenv("MCB200_VERLET_MIN_N")) vl_min_n = atoi(mn);   // tests lower it to run k_run_vl on N = 240
+    if (!h->energy_only && !g.mat_in_image && g.N >= vl_min_n && g.N > 32 && g.N < 65536 && h->spec_w == 1 && h->spec_gl == 32 && !getenv("MCB200_NO_VERLET")) {
+        // large box, one step per warp: neighbour lists for k_run_vl (mcb_verlet.cuh)
+        h->vl.skin = 2.0;
+        if (const char *sk = getenv("MCB200_SKIN")) { double v = atof(sk); if (v > 0.0) h->vl.skin = v; }   // tests shrink it to force rebuilds
+        CKC(cudaMalloc(&h->vl.idx, nc * (size_t)g.N * VL_K * sizeof(unsigned short)));
+        CKC(cudaMalloc(&h->vl.cnt, nc * (size_t)(g.N + 1) * sizeof(int)));
+        CKC(cudaMalloc(&h->vl.ref, nc * (size_t)3 * g.Np * sizeof(double)));
+        CKC(cudaMemset(h->vl.cnt, 0, nc * (size_t)(g.N + 1) * sizeof(int)));
     }
     CKC(cudaMalloc(&h->work, nc * g.work_doubles * sizeof(double)));
     CKC(cudaMemset(h->work, 0, nc * g.work_doubles * sizeof(double)));
@@ -633,7 +649,11 @@ extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, i
     if (uniforms) { if (h->coul) launch_run_ubuf<true>(h, nsteps, cap, d_consumed, d_steps); else launch_run_ubuf<false>(h, nsteps, cap, d_consumed, d_steps); }
     else {
         CK(h, cudaMemsetAsync(d_consumed, 0, sizeof(long long) * nc, h->stream));
-        if (h->coul) launch_run_spec_any<true>(h, nsteps, d_steps); else launch_run_spec_any<false>(h, nsteps, d_steps);
+        if (h->vl.idx) {
+            set_smem_attr(h, k_run_vl<true>, h->smem_spec_bytes); set_smem_attr(h, k_run_vl<false>, h->smem_spec_bytes);
+            if (h->coul) k_run_vl<true><<<h->n_chains, 32, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);
+            else k_run_vl<false><<<h->n_chains, 32, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);
+        } else if (h->coul) launch_run_spec_any<true>(h, nsteps, d_steps); else launch_run_spec_any<false>(h, nsteps, d_steps);
     }
     h->launches++;
     CK(h, cudaGetLastError());

@@ -39,7 +39,7 @@ struct Geo {
     int spec_group_doubles; // stride between the work areas of the look-ahead groups of k_run_spec (= work_doubles)
     int mat_in_image;
     int quirk31;
-    double boxl, boxl2, inv_boxl, cut2, conv;
+    double boxl, boxl2, inv_boxl, cut2, conv, cutoff;
 };
 
 // Scalars of one chain (the driver's TOTENG, DPOSMAX, NSUC, ... MonteCarlo.F90:33-47,98-101).

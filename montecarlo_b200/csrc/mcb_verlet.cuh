@@ -1,0 +1,273 @@
+// mcb_verlet.cuh — batched stepping for LARGE boxes (N > 32, pair matrix in global memory): k_run_vl.
+//
+// Same Markov chain as k_run_spec with one step in flight (same ring of pre-drawn moves, same arithmetic, same
+// commit), but nothing in a step is O(N) any more.  Every molecule keeps a list of the molecules whose centre of
+// mass was within cutoff + skin when the lists were built (a Verlet list, in global memory: it is read once per
+// step, right after the molecule is known, and has arrived long before the gate needs it).  While no molecule has
+// strayed more than skin/2 from where it was at build time, every partner inside the cutoff of a trial position is
+// on the moved molecule's list, so the centre-of-mass gate (MonteCarlo.F90:804-813), the old matrix row needed for
+// the row-sum bookkeeping and the "left the cutoff" test only look at the ~25 listed candidates instead of all N
+// molecules.  The list only decides WHICH pairs get the reference's exact gate test; a trial position further than
+// skin/2 from the build position (or a molecule whose list overflowed) falls back to the full scan for that step,
+// and an accepted move beyond skin/2 rebuilds all lists.  Requires every centre of mass inside [-BOXL, BOXL]
+// (true after the wrap at :710-712), otherwise the reference's minimum image is not a metric and lists stay off.
+#pragma once
+
+#include "mcb_kernels.cuh"
+
+namespace mcb {
+
+constexpr int VL_K = 64;   // list capacity per molecule (two 32-lane chunks); cutoff 7 + skin 2 holds ~25 in liquid DMSO
+
+struct VerletBufs { unsigned short *idx; int *cnt; double *ref; double skin; };   // per chain: idx[N][VL_K], cnt[N], ref[3][Np]
+
+template <bool COUL>
+__global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl,
+                                               long long nsteps, long long *out_steps, VerletBufs vb)
+{
+    extern __shared__ __align__(16) double smem[];
+    const int lane = threadIdx.x;
+    const int c = blockIdx.x;
+    const int N = g.N, Np = g.Np, MS = g.MS, nsolp = g.nsolp;
+    const unsigned lt = (1u << lane) - 1u;
+    double *gimg = images + (size_t)c * g.image_doubles;
+    double *img = smem;
+    {
+        const double2 *src = reinterpret_cast<const double2 *>(gimg);
+        double2 *dst = reinterpret_cast<double2 *>(img);
+        for (int k = lane; k < g.stage_doubles / 2; k += 32) dst[k] = src[k];
+    }
+    double *const mat = matg + (size_t)c * N * MS;
+    double *const com = img + g.o_com, *const hoek = img + g.o_hoek, *const energy = img + g.o_energy;
+    double *const sites = img + g.o_sites;
+    const double *const tabAB = img + g.o_tabAB, *const tabQ = img + g.o_tabQ;
+    const int a = lane & 3, sub = lane >> 2;
+    double *const wk = smem + g.stage_doubles;
+    int *const list = reinterpret_cast<int *>(wk + g.o_list);
+    double *const epart = wk + g.o_epart;
+    double *const ring_thr = wk + g.spec_group_doubles + SPECX_DOUBLES;   // same shared-memory plan as k_run_spec, T = 1
+    double *const ring_rv = ring_thr + 64;
+    int *const ring_i = reinterpret_cast<int *>(ring_rv + 6 * 64);
+    double *const rowsum = ring_rv + 6 * 64 + 32;
+    unsigned short *const vidx = vb.idx + (size_t)c * N * VL_K;
+    int *const vcnt = vb.cnt + (size_t)c * (N + 1);
+    double *const vref = vb.ref + (size_t)c * 3 * Np;
+    const double rl = g.cutoff + vb.skin, rl2 = rl * rl, h2 = 0.25 * vb.skin * vb.skin;
+    ChainCtl s = ctl[c];
+    for (int p = lane; p < nsolp; p += 32) list[p] = N + p;
+    __syncwarp();
+    for (int j = lane; j < N; j += 32) {   // row sums from the stored matrix (symmetric: column sums, coalesced)
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+        int i = 0;
+        for (; i + 3 < N; i += 4) {
+            a0 += mat[(size_t)i * MS + j]; a1 += mat[(size_t)(i + 1) * MS + j];
+            a2 += mat[(size_t)(i + 2) * MS + j]; a3 += mat[(size_t)(i + 3) * MS + j];
+        }
+        for (; i < N; ++i) a0 += mat[(size_t)i * MS + j];
+        rowsum[j] = (a0 + a1) + (a2 + a3);
+    }
+    __syncwarp();
+    {
+        double acc = 0.0;
+        for (int i = lane; i < N; i += 32) acc += fma(0.5, rowsum[i], energy[i]);
+        s.toteng = warp_sum(acc);
+    }
+    // lists are usable only if the reference's minimum image is a true metric: all centres of mass inside the box
+    bool inside = true;
+    for (int j = lane; j < N; j += 32) inside = inside && fabs(com[j]) <= g.boxl && fabs(com[Np + j]) <= g.boxl && fabs(com[2 * Np + j]) <= g.boxl;
+    const bool lists_on = __all_sync(FULL, inside);
+    bool need_rebuild = lists_on;
+
+    const double relx = rel.r[3 * a], rely = rel.r[3 * a + 1], relz = rel.r[3 * a + 2];
+    const int wpair = rel.n_sites * rel.n_sites, wsol = rel.n_sites * g.nsol;
+    const double neg_inv_rt = -1000.0 / (8.314 * s.temperature);
+    const int rr = min(max(lane - 1, 0), 5);
+    const bool isang = rr >= 3;
+    const int k = isang ? rr - 3 : rr;
+    double *const base = (isang ? hoek : com) + k * Np;
+    const double period = isang ? TAU_D : g.boxl2, half = isang ? PI_D : g.boxl;
+    const double inv_half = isang ? 1.0 / PI_D : g.inv_boxl;
+    int adj_count = (int)(s.step % s.nadj);
+    int done = 0;
+    unsigned nsuc = 0, nacc = (unsigned)s.naccept, racc = 0, nclamp = 0, uused = 0, prod_acc = 0, nstat = 0, nrebuild = 0;
+    unsigned long long sitepairs = 0;
+    const unsigned long long step0 = (unsigned long long)s.step;
+    const int nsteps_i = (int)min(nsteps, (long long)0x3fffffff);
+    unsigned long long gen_end = step0;
+
+    while (done < nsteps_i) {
+        if (need_rebuild) {
+            // ---- (re)build every list from the current centres of mass, which become the reference positions
+            for (int j = lane; j < 3 * Np; j += 32) vref[j] = com[j];
+            for (int m = 0; m < N; ++m) {
+                const double mx = com[m], my = com[Np + m], mz = com[2 * Np + m];
+                int cnt = 0;
+                for (int c0 = 0; c0 < N; c0 += 32) {
+                    const int j = c0 + lane;
+                    const bool in = j < N && j != m && !(pair_r2(com[j] - mx, com[Np + j] - my, com[2 * Np + j] - mz, g) > rl2);
+                    const unsigned b = __ballot_sync(FULL, in);
+                    const int pos = cnt + __popc(b & lt);
+                    if (in && pos < VL_K) vidx[(size_t)m * VL_K + pos] = (unsigned short)j;
+                    cnt += __popc(b);
+                }
+                if (lane == 0) vcnt[m] = cnt > VL_K ? -1 : cnt;
+            }
+            need_rebuild = false;
+            nrebuild++;
+            __syncwarp();
+        }
+        while (step0 + (unsigned)done + 1 > gen_end) {   // pre-draw the next 32 steps, one step per lane (as k_run_spec)
+            const unsigned long long sidx = gen_end + (unsigned)lane;
+            const int e = (int)(sidx & 63ULL);
+            const double u0 = stream_uniform(s.rng_key, 8ULL * sidx);
+            int ii = (int)(u0 * (double)N) + 1;                     // MCINIT, MonteCarlo.F90:697-698
+            if (g.quirk31 && ii == 31) ii = 30;
+            ring_i[e] = min(ii, N) - 1;
+#pragma unroll
+            for (int q = 0; q < 6; ++q) {
+                const double rvu = (stream_uniform(s.rng_key, 8ULL * sidx + 1 + q) - 0.5) * 2.0;
+                ring_rv[6 * e + q] = (q < 3 ? INV_SQRT3 : 1.0) * rvu;
+            }
+            ring_thr[e] = log(stream_uniform(s.rng_key, 8ULL * sidx + 7)) * (1.0 / LN_E_F32);
+            gen_end += 32;
+            __syncwarp();
+        }
+        const int ring_e = (int)((step0 + (unsigned)done) & 63ULL);
+        const int i = ring_i[ring_e];
+        const double thr = ring_thr[ring_e];
+        const double old_tot = rowsum[i] + energy[i];
+        const double old_part = lane == 0 ? old_tot : 0.0;
+        // ---- candidates of molecule i and their old matrix entries: issued now, used by the gate / the commit
+        const int cnt = lists_on ? vcnt[i] : -1;
+        int cj[2];
+        double cold[2];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int ci = lane + 32 * q;
+            cj[q] = ci < cnt ? (int)vidx[(size_t)i * VL_K + ci] : -1;
+        }
+        const double rfx = lists_on ? vref[i] : 0.0, rfy = lists_on ? vref[Np + i] : 0.0, rfz = lists_on ? vref[2 * Np + i] : 0.0;
+#pragma unroll
+        for (int q = 0; q < 2; ++q) cold[q] = cj[q] >= 0 ? mat[(size_t)i * MS + cj[q]] : 0.0;
+        // ---- trial move (MCINIT :699-712), RotMatrix of the own site
+        const double rv = (isang ? s.dhoekmax : s.dposmax) * ring_rv[6 * ring_e + rr];
+        const double nv = wrap_checked(base[i] + rv, period, half, inv_half);
+        double sn, cs;
+        sincos_small(nv, sn, cs);
+        const double ncx = shfl_d(nv, 1), ncy = shfl_d(nv, 2), ncz = shfl_d(nv, 3);
+        const double c1 = shfl_d(cs, 4), s1 = shfl_d(sn, 4), c2 = shfl_d(cs, 5), s2 = shfl_d(sn, 5), c3 = shfl_d(cs, 6), s3 = shfl_d(sn, 6);
+        double sx, sy, sz;
+        rotate_site(c1, s1, c2, s2, c3, s3, relx, rely, relz, ncx, ncy, ncz, sx, sy, sz);
+        // is the trial position still covered by the list?  (same value on every lane)
+        const bool far = !lists_on || pair_r2(ncx - rfx, ncy - rfy, ncz - rfz, g) > h2;
+        const bool use_list = cnt >= 0 && !far;
+        // ---- centre-of-mass gate (:804-813) on the candidates, or on everybody
+        int nn = 0;
+        bool cin[2] = {false, false};
+        if (use_list) {
+#pragma unroll
+            for (int q = 0; q < 2; ++q)
+                if (cj[q] >= 0) cin[q] = !(pair_r2(com[cj[q]] - ncx, com[Np + cj[q]] - ncy, com[2 * Np + cj[q]] - ncz, g) > g.cut2);
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const unsigned b = __ballot_sync(FULL, cin[q]);
+                if (cin[q]) list[nsolp + nn + __popc(b & lt)] = cj[q];
+                nn += __popc(b);
+            }
+        } else {
+            for (int c0 = 0; c0 < N; c0 += 32) {
+                const int j = c0 + lane;
+                const bool in = j < N && j != i && !(pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2);
+                const unsigned b = __ballot_sync(FULL, in);
+                if (in) list[nsolp + nn + __popc(b & lt)] = j;
+                nn += __popc(b);
+            }
+        }
+        __syncwarp();
+        // ---- site pairs (calcLJ / CalcLJ_SV), staged
+        const int nslots = nsolp + nn;
+        double lane_tot = 0.0;
+        for (int s0 = sub; s0 < nslots; s0 += 2 * 8)
+            lane_tot += items_staged<COUL, 2>(g, sites, tabAB, tabQ, list, nsolp, nslots, s0, 8, a, sx, sy, sz, epart);
+        double dE = lane_tot - old_part, esol = 0.0;
+        __syncwarp();
+        for (int p = sub; p < nsolp; p += 8) esol += epart[4 * p + a];
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
+        // ---- METROPOLIS (:720-788) on DELTA = dE
+        const double exponent = dE * neg_inv_rt;
+        const bool clamped = !(fabs(dE) <= DBL_HUGE);
+        const bool used8 = !clamped && exponent >= -75.0 && exponent < 0.0;
+        const bool accept = !clamped && (exponent >= 0.0 || (used8 && thr <= exponent));
+        if (accept) {
+            // partners that left the cutoff: entry to zero, their row sums lose the old pair energy
+            if (use_list) {
+#pragma unroll
+                for (int q = 0; q < 2; ++q)
+                    if (cold[q] != 0.0 && !cin[q]) {
+                        const int j = cj[q];
+                        rowsum[j] -= cold[q];
+                        mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0;
+                    }
+            } else {
+                for (int j = lane; j < N; j += 32) {
+                    const double old = mat[(size_t)i * MS + j];
+                    if (old != 0.0 && j != i && pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2) {
+                        rowsum[j] -= old;
+                        mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0;
+                    }
+                }
+            }
+            // partners inside the cutoff: SS(i,j) = SS(j,i) = EN (:819-820), row sums follow
+            for (int sl = nsolp + lane; sl < nslots; sl += 32) {
+                const int j = list[sl];
+                const double e = (epart[4 * sl] + epart[4 * sl + 1]) + (epart[4 * sl + 2] + epart[4 * sl + 3]);
+                rowsum[j] += e - mat[(size_t)i * MS + j];
+                mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
+            }
+            if (lane >= 1 && lane <= 6) base[i] = nv;
+            if (lane < 4) {
+                sites[SITE_DOUBLES * i + 3 * a] = sx; sites[SITE_DOUBLES * i + 3 * a + 1] = sy; sites[SITE_DOUBLES * i + 3 * a + 2] = sz;
+            }
+            if (lane == 0) { energy[i] = esol; rowsum[i] = (dE + old_tot) - esol; }
+            if (lists_on && far) need_rebuild = true;   // the molecule now sits more than skin/2 from its build position
+        }
+        // ---- bookkeeping
+        uused += 7 + (used8 ? 1 : 0);
+        nclamp += clamped ? 1 : 0;
+        sitepairs += (unsigned)(wpair * nn + wsol);
+        s.last_delta = dE;
+        const bool in_prod = (long long)(step0 + (unsigned)done + 1ULL) >= s.start_prod;
+        if (accept) {
+            nsuc++; nacc++;
+            s.toteng += dE;
+            if (in_prod) { s.production += s.toteng; prod_acc++; }
+        }
+        if (in_prod) { s.sum_e += s.toteng; s.sum_e2 = fma(s.toteng, s.toteng, s.sum_e2); nstat++; }
+        racc = nacc;
+        if (++adj_count == s.nadj) {                                // mod(I, NADJ) == 0, :766-777
+            adj_count = 0;
+            const double ratio = (double)((float)nacc / (float)s.nadj);
+            if (ratio > 0.5) { s.dposmax *= (1.0 + s.padj); s.dhoekmax *= (1.0 + s.padj); }
+            else if (ratio < 0.5) { s.dposmax *= (1.0 - s.padj); s.dhoekmax *= (1.0 - s.padj); }
+            s.dposmax = fmax(s.dposmax, s.dposmin); s.dhoekmax = fmax(s.dhoekmax, s.dhoekmin);
+            nacc = 0;
+        }
+        ++done;
+        __syncwarp();
+    }
+    {
+        const int n_mut = g.o_sites + SITE_DOUBLES * N;
+        for (int qq = lane; qq < n_mut; qq += 32) gimg[qq] = img[qq];
+    }
+    if (lane == 0) {
+        s.step += done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.uused += uused; s.prod_acc += prod_acc;
+        s.nstat += nstat; s.sitepairs += (long long)sitepairs;
+        if (done > 0) s.ratio = (double)((float)racc / (float)s.nadj);
+        ctl[c] = s;
+        if (out_steps) out_steps[c] = done;
+        vcnt[N] = (int)nrebuild;   // diagnostic: list rebuilds in this launch (slot N of the count array)
+    }
+}
+
+}  // namespace mcb

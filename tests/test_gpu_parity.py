@@ -271,6 +271,54 @@ def test_batched_mode_replica_box(shipped, matrix_mode, lookahead):
         _compare_chain(st, c, o.stats(), com, hoek, o)
 
 
+@pytest.mark.parametrize("skin", ["0.25", "1.0", None])
+def test_large_box_neighbour_lists(shipped, skin, monkeypatch):
+    """N = 240 runs through k_run_vl (Verlet lists in global memory).  A tiny skin forces the fall-back to the full
+    scan and list rebuilds every few accepted moves; the chain must stay the oracle's either way, and equal to the
+    list-free kernel's."""
+    box, system = shipped
+    b = boxio.replicate(box, 2)
+    s = _sys_for(system, b)
+    monkeypatch.setenv("MCB200_VERLET_MIN_N", "33")     # by default the lists start at N > 256
+    if skin is None:
+        monkeypatch.setenv("MCB200_NO_VERLET", "1")
+    else:
+        monkeypatch.setenv("MCB200_SKIN", skin)
+    nch, nsteps = 2, 6000
+    eng = _engine(s, b.n, n_chains=nch)
+    eng.set_state(b.com, b.hoek)
+    eng.seed(np.array([21, 22], dtype=np.uint64))
+    eng.run_steps(nsteps // 2)
+    eng.run_steps(nsteps // 2)
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    for c in range(nch):
+        o = ol.OracleChain(s, b.com, b.hoek)
+        o.total_energy()
+        o.run_steps_rng(nsteps, ol.rng_seed(21 + c), trace=False)
+        _compare_chain(st, c, o.stats(), com, hoek, o)
+    fresh = eng.total_energy()[0]
+    assert np.all(np.abs(fresh - st["toteng"]) <= RTOL * np.abs(fresh))
+
+
+def test_neighbour_lists_default_size(shipped):
+    """N = 810 (3x3x3 replica): k_run_vl by default; 1500 steps of two chains against the oracle."""
+    box, system = shipped
+    b = boxio.replicate(box, 3)
+    s = _sys_for(system, b)
+    eng = _engine(s, b.n, n_chains=2)
+    eng.set_state(b.com, b.hoek)
+    eng.seed(np.array([5, 6], dtype=np.uint64))
+    eng.run_steps(1500)
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    for c in range(2):
+        o = ol.OracleChain(s, b.com, b.hoek)
+        o.total_energy()
+        o.run_steps_rng(1500, ol.rng_seed(5 + c), trace=False)
+        _compare_chain(st, c, o.stats(), com, hoek, o)
+
+
 def test_per_chain_solute_conformers(shipped):
     """Config 4 shape: every chain sees its own solute coordinates."""
     box, system = shipped
