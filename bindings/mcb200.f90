@@ -75,5 +75,18 @@ module mcb200
       import; type(c_ptr), value :: h; integer(c_int), value :: chain0, nchains
       type(mcb_chain_stats), intent(out) :: stats(*)
     end function
+    integer(c_int) function mcb_row_energy(h, chain, i, ss_row, e_i) bind(C, name="mcb_row_energy")
+      import; type(c_ptr), value :: h; integer(c_int), value :: chain, i
+      real(c_double), intent(out) :: ss_row(*), e_i
+    end function
+    integer(c_int) function mcb_reset_stats(h, chain0, nchains) bind(C, name="mcb_reset_stats")
+      import; type(c_ptr), value :: h; integer(c_int), value :: chain0, nchains
+    end function
+    integer(c_int) function mcb_box_energy_noalloc(p, d_com, d_hoek, solute, sol_tab, d_out, stream, errbuf, errlen) &
+        bind(C, name="mcb_box_energy_noalloc")   ! d_com, d_hoek, d_out: DEVICE pointers owned by the caller
+      import; type(mcb_params), intent(in) :: p; type(c_ptr), value :: d_com, d_hoek, d_out, stream
+      real(c_double), intent(in) :: solute(*), sol_tab(*)
+      character(kind=c_char) :: errbuf(*); integer(c_size_t), value :: errlen
+    end function
   end interface
 end module mcb200
