@@ -156,16 +156,18 @@ __device__ unsigned long long g_phase[8];
 #define PH_T(k) do { } while (0)
 #endif
 
-// x - period*AINT(x/half) with the quotient formed by a multiplication; when the product lands within 1e-13
-// of an integer (where the rounding of x/half could matter) the true division decides, so the result is
-// always the one the reference's expression gives (MonteCarlo.F90:705-712, :808-810).
-__device__ __forceinline__ double wrap_checked(double x, double period, double half, double inv_half)
+// x - period*AINT(x/half) (MonteCarlo.F90:705-712) without a division and without a branch.  q0 = x*(1/half) is
+// within an ulp of the quotient; the residual x - q0*half is exact in one fma, and q0 + r*(1/half) then rounds to the
+// correctly rounded x/half (Markstein's division step; 1/half is the correctly rounded reciprocal, formed by a true
+// division on the host or at compile time), so AINT sees exactly the reference's quotient.  A guarded true division
+// (a function call) in the middle of the step's straight-line code cost 1.4 % of the step.
+// tests/test_abi_cpu.py::test_wrap_fma_matches_division checks the identity on the host, adversarial cases included.
+__device__ __forceinline__ double wrap_fma(double x, double period, double half, double inv_half)
 {
-    double q = x * inv_half;
-    double t = trunc(q);
-    double f = fabs(q - t);
-    if (f < 1e-13 || f > 1.0 - 1e-13) t = trunc(x / half);
-    return fma(-period, t, x);
+    const double q0 = x * inv_half;
+    const double r = fma(-q0, half, x);
+    const double q = fma(r, inv_half, q0);
+    return fma(-period, trunc(q), x);
 }
 
 // One (partner, own site a) item: own site (sx,sy,sz) against the four sites of virtual molecule vm with the
@@ -347,7 +349,7 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
         double rv = (myu - 0.5) * 2.0;
         rv = f1 * rv;
         rv = (isang ? s.dhoekmax : s.dposmax) * rv;
-        const double nv = wrap_checked(base[i] + rv, period, half, inv_half);
+        const double nv = wrap_fma(base[i] + rv, period, half, inv_half);
         double sn, cs;
         sincos(nv, &sn, &cs);
         const double ncx = shfl_d(nv, 1), ncy = shfl_d(nv, 2), ncz = shfl_d(nv, 3);
@@ -476,8 +478,10 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
 struct SpecX { double dE, esol, ncx, ncy, ncz; int i, nn, flags, pad; };   // what a step hands to the resolution
 constexpr int SPECX_DOUBLES = sizeof(SpecX) / 8;
 
+// With W > 1 the block must still fit 7 times on an SM (1024 chains / 148 SMs): without the minimum-blocks hint the
+// kernel takes ~155 registers, 64-thread blocks fit only 6 times and the 1024 chains need a second wave.
 template <bool COUL, bool MAT_SMEM, int GL, int W, bool SMALL>
-__global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl,
+__global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl,
                                                      long long nsteps, long long *out_steps)
 {
     constexpr int G = 32 / GL;          // steps per warp
@@ -607,7 +611,7 @@ __global__ void __launch_bounds__(32 * W) k_run_spec(Geo g, SiteRel rel, double 
                 }
         }
         const double rv = (isang ? s.dhoekmax : s.dposmax) * ring_rv[6 * ring_e + rr];
-        const double nv = wrap_checked(base[i] + rv, period, half, inv_half);   // :699-712
+        const double nv = wrap_fma(base[i] + rv, period, half, inv_half);       // :699-712
         double sn, cs;
         sincos_small(nv, sn, cs);
         const double ncx = shfl_d(nv, leader + 1), ncy = shfl_d(nv, leader + 2), ncz = shfl_d(nv, leader + 3);

@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
         for (int q = 0; q < 2; ++q) cold[q] = cj[q] >= 0 ? mat[(size_t)i * MS + cj[q]] : 0.0;
         // ---- trial move (MCINIT :699-712), RotMatrix of the own site
         const double rv = (isang ? s.dhoekmax : s.dposmax) * ring_rv[6 * ring_e + rr];
-        const double nv = wrap_checked(base[i] + rv, period, half, inv_half);
+        const double nv = wrap_fma(base[i] + rv, period, half, inv_half);
         double sn, cs;
         sincos_small(nv, sn, cs);
         const double ncx = shfl_d(nv, 1), ncy = shfl_d(nv, 2), ncz = shfl_d(nv, 3);

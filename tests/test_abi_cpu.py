@@ -50,3 +50,30 @@ def test_product_does_not_touch_the_oracle():
             text = p.read_text()
             assert "oracle" not in text.lower(), p
     assert "oracle" not in (ROOT / "include" / "mcb200.h").read_text().lower()
+
+
+def test_wrap_fma_matches_division():
+    """k_run_spec wraps coordinates with wrap_fma (mcb_kernels.cuh): x - period*AINT(q) with q = q0 + r/half formed by
+    two fmas instead of the reference's x/half (MonteCarlo.F90:705-712).  The host check of the identity AINT(q) ==
+    AINT(x/half): random arguments and the adversarial ones, x within a few ulps of k*half, for the half-widths the
+    kernels use (pi for the angles, BOXL for the box)."""
+    libm = C.CDLL("libm.so.6")
+    libm.fma.restype = C.c_double
+    libm.fma.argtypes = [C.c_double] * 3
+    rng = np.random.default_rng(7)
+    for half in (np.pi, 7.7838685668, 15.5677371336, 23.3516057004, 9.3):
+        inv = 1.0 / half
+        xs = list((rng.random(4000) - 0.5) * 8.0 * half)
+        for k in range(-4, 5):
+            for ul in range(-4, 5):
+                x = np.float64(k * half)
+                for _ in range(abs(ul)):
+                    x = np.nextafter(x, np.inf if ul > 0 else -np.inf)
+                xs.append(float(x))
+        for x in xs:
+            q0 = x * inv
+            r = libm.fma(-q0, half, x)
+            q = libm.fma(r, inv, q0)
+            assert np.trunc(q) == np.trunc(x / half), (x, half)
+            if abs(x) > 1e-300:
+                assert q == x / half, (x, half)
