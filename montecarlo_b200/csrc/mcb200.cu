@@ -206,18 +206,19 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
         CKC(cudaMalloc(&h->big_out, sizeof(double) * 2));
         CKC(cudaMalloc(&h->big_nout, sizeof(long long)));
     }
-    // neighbour lists pay once the gate has more than ~8 chunks of 32 molecules to scan: at N = 240 k_run_spec's chunked
-    // gate is as fast (4.6e10 vs 4.5e10 site pairs/s), at N = 810 the lists are 3x faster (profiles/other_configs_r01.txt)
-    int vl_min_n = 257;
-    if (const char *mn = getenv("MCB200_VERLET_MIN_N")) vl_min_n = atoi(mn);   // tests lower it to run k_run_vl on N = 240
+    // neighbour lists for every box whose pair matrix lives in global memory: with the next step's list fetched one
+    // step ahead they win from the smallest such box on (N = 240: 6.0e10 vs 4.75e10 site pairs/s for the full scan,
+    // N = 810: 1.2e10 vs 3e9; profiles/other_configs_r01.txt)
+    int vl_min_n = 33;
+    if (const char *mn = getenv("MCB200_VERLET_MIN_N")) vl_min_n = atoi(mn);   // tuning only
     if (!h->energy_only && !g.mat_in_image && g.N >= vl_min_n && g.N > 32 && g.N < 65536 && h->spec_w == 1 && h->spec_gl == 32 && !getenv("MCB200_NO_VERLET")) {
         // large box, one step per warp: neighbour lists for k_run_vl (mcb_verlet.cuh)
         h->vl.skin = 2.0;
         if (const char *sk = getenv("MCB200_SKIN")) { double v = atof(sk); if (v > 0.0) h->vl.skin = v; }   // tests shrink it to force rebuilds
         CKC(cudaMalloc(&h->vl.idx, nc * (size_t)g.N * VL_K * sizeof(unsigned short)));
-        CKC(cudaMalloc(&h->vl.cnt, nc * (size_t)(g.N + 1) * sizeof(int)));
+        CKC(cudaMalloc(&h->vl.cnt, nc * (size_t)(g.N + 2) * sizeof(int)));
         CKC(cudaMalloc(&h->vl.ref, nc * (size_t)3 * g.Np * sizeof(double)));
-        CKC(cudaMemset(h->vl.cnt, 0, nc * (size_t)(g.N + 1) * sizeof(int)));
+        CKC(cudaMemset(h->vl.cnt, 0, nc * (size_t)(g.N + 2) * sizeof(int)));
     }
     CKC(cudaMalloc(&h->work, nc * g.work_doubles * sizeof(double)));
     CKC(cudaMemset(h->work, 0, nc * g.work_doubles * sizeof(double)));
@@ -315,6 +316,7 @@ extern "C" int mcb_set_chain_state(mcb_t *h, int chain0, int nchains, const doub
 {
     if (int rc = check_range(h, chain0, nchains)) return rc;
     if (!com || !hoek) return arg_err(h, "mcb_set_chain_state: null array");
+    h->vl.trust = 0;   // new coordinates: the neighbour lists of k_run_vl are rebuilt at the next launch
     const Geo &g = h->g;
     CK(h, cudaSetDevice(h->device));
     const int w = 6 * g.Np;   // com planes + hoek planes are adjacent at the head of the image
@@ -477,6 +479,7 @@ extern "C" int mcb_commit(mcb_t *h, int nchains, const unsigned char *accept)
     if (int rc = check_range(h, 0, nchains)) return rc;
     if (!accept) return arg_err(h, "mcb_commit: null array");
     if (h->energy_only) return arg_err(h, "mcb_commit: this handle is in energy-only mode");
+    h->vl.trust = 0;
     CK(h, cudaSetDevice(h->device));
     CK(h, cudaMemcpyAsync(h->d_acc, accept, nchains, cudaMemcpyHostToDevice, h->stream));
     k_commit<<<nchains, 32, 0, h->stream>>>(h->g, h->images, h->matg, h->work, h->ctl, h->d_acc);
@@ -646,6 +649,7 @@ extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, i
     }
     long long *d_consumed = h->d_ll, *d_steps = h->d_ll + nc;
     if (nsteps > (1LL << 30)) return arg_err(h, "mcb_run_steps: at most 2^30 steps per call");
+    if (uniforms) h->vl.trust = 0;   // k_run_steps moves molecules without looking at the lists
     if (uniforms) { if (h->coul) launch_run_ubuf<true>(h, nsteps, cap, d_consumed, d_steps); else launch_run_ubuf<false>(h, nsteps, cap, d_consumed, d_steps); }
     else {
         CK(h, cudaMemsetAsync(d_consumed, 0, sizeof(long long) * nc, h->stream));
@@ -653,6 +657,7 @@ extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, i
             set_smem_attr(h, k_run_vl<true>, h->smem_spec_bytes); set_smem_attr(h, k_run_vl<false>, h->smem_spec_bytes);
             if (h->coul) k_run_vl<true><<<h->n_chains, 32, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);
             else k_run_vl<false><<<h->n_chains, 32, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);
+            h->vl.trust = 1;   // until an entry point other than this one changes the coordinates
         } else if (h->coul) launch_run_spec_any<true>(h, nsteps, d_steps); else launch_run_spec_any<false>(h, nsteps, d_steps);
     }
     h->launches++;

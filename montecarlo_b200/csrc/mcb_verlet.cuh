@@ -2,8 +2,8 @@
 //
 // Same Markov chain as k_run_spec with one step in flight (same ring of pre-drawn moves, same arithmetic, same
 // commit), but nothing in a step is O(N) any more.  Every molecule keeps a list of the molecules whose centre of
-// mass was within cutoff + skin when the lists were built (a Verlet list, in global memory: it is read once per
-// step, right after the molecule is known, and has arrived long before the gate needs it).  While no molecule has
+// mass was within cutoff + skin when the lists were built (a Verlet list, in global memory: the moved molecule of
+// the next step is known from the ring of pre-drawn moves, so its list is fetched one step ahead).  While no molecule has
 // strayed more than skin/2 from where it was at build time, every partner inside the cutoff of a trial position is
 // on the moved molecule's list, so the centre-of-mass gate (MonteCarlo.F90:804-813), the old matrix row needed for
 // the row-sum bookkeeping and the "left the cutoff" test only look at the ~25 listed candidates instead of all N
@@ -19,7 +19,9 @@ namespace mcb {
 
 constexpr int VL_K = 64;   // list capacity per molecule (two 32-lane chunks); cutoff 7 + skin 2 holds ~25 in liquid DMSO
 
-struct VerletBufs { unsigned short *idx; int *cnt; double *ref; double skin; };   // per chain: idx[N][VL_K], cnt[N], ref[3][Np]
+// per chain: idx[N][VL_K], cnt[N + 2] (slot N: rebuilds in the last launch; slot N+1: lists match the stored coordinates), ref[3][Np]
+// trust: nothing but k_run_vl has changed the coordinates since the last launch, so valid lists are kept across launches
+struct VerletBufs { unsigned short *idx; int *cnt; double *ref; double skin; int trust; };
 
 template <bool COUL>
 __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl,
@@ -50,7 +52,7 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
     int *const ring_i = reinterpret_cast<int *>(ring_rv + 6 * 64);
     double *const rowsum = ring_rv + 6 * 64 + 32;
     unsigned short *const vidx = vb.idx + (size_t)c * N * VL_K;
-    int *const vcnt = vb.cnt + (size_t)c * (N + 1);
+    int *const vcnt = vb.cnt + (size_t)c * (N + 2);
     double *const vref = vb.ref + (size_t)c * 3 * Np;
     const double rl = g.cutoff + vb.skin, rl2 = rl * rl, h2 = 0.25 * vb.skin * vb.skin;
     ChainCtl s = ctl[c];
@@ -76,7 +78,7 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
     bool inside = true;
     for (int j = lane; j < N; j += 32) inside = inside && fabs(com[j]) <= g.boxl && fabs(com[Np + j]) <= g.boxl && fabs(com[2 * Np + j]) <= g.boxl;
     const bool lists_on = __all_sync(FULL, inside);
-    bool need_rebuild = lists_on;
+    bool need_rebuild = lists_on && !(vb.trust && vcnt[N + 1] == 1);
 
     const double relx = rel.r[3 * a], rely = rel.r[3 * a + 1], relz = rel.r[3 * a + 2];
     const int wpair = rel.n_sites * rel.n_sites, wsol = rel.n_sites * g.nsol;
@@ -94,6 +96,10 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
     const unsigned long long step0 = (unsigned long long)s.step;
     const int nsteps_i = (int)min(nsteps, (long long)0x3fffffff);
     unsigned long long gen_end = step0;
+    // list of the NEXT step's molecule (known from the ring), fetched one step ahead: count, candidates, build position
+    int p_cnt = -1, p_idx[2] = {0, 0};
+    double p_rfx = 0.0, p_rfy = 0.0, p_rfz = 0.0;
+    bool p_valid = false;
 
     while (done < nsteps_i) {
         if (need_rebuild) {
@@ -113,10 +119,11 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
                 if (lane == 0) vcnt[m] = cnt > VL_K ? -1 : cnt;
             }
             need_rebuild = false;
+            p_valid = false;
             nrebuild++;
             __syncwarp();
         }
-        while (step0 + (unsigned)done + 1 > gen_end) {   // pre-draw the next 32 steps, one step per lane (as k_run_spec)
+        while (step0 + (unsigned)done + 2 > gen_end) {   // pre-draw the next 32 steps, one step per lane (as k_run_spec)
             const unsigned long long sidx = gen_end + (unsigned)lane;
             const int e = (int)(sidx & 63ULL);
             const double u0 = stream_uniform(s.rng_key, 8ULL * sidx);
@@ -137,18 +144,28 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
         const double thr = ring_thr[ring_e];
         const double old_tot = rowsum[i] + energy[i];
         const double old_part = lane == 0 ? old_tot : 0.0;
-        // ---- candidates of molecule i and their old matrix entries: issued now, used by the gate / the commit
-        const int cnt = lists_on ? vcnt[i] : -1;
+        // ---- candidates of molecule i: fetched during the previous step (global memory, two dependent round trips
+        //      otherwise); their old matrix entries are issued now and only needed by the commit
+        if (lists_on && !p_valid) {
+            p_cnt = vcnt[i];
+            p_idx[0] = (int)vidx[(size_t)i * VL_K + lane]; p_idx[1] = (int)vidx[(size_t)i * VL_K + 32 + lane];
+            p_rfx = vref[i]; p_rfy = vref[Np + i]; p_rfz = vref[2 * Np + i];
+        }
+        const int cnt = lists_on ? p_cnt : -1;
         int cj[2];
         double cold[2];
 #pragma unroll
-        for (int q = 0; q < 2; ++q) {
-            const int ci = lane + 32 * q;
-            cj[q] = ci < cnt ? (int)vidx[(size_t)i * VL_K + ci] : -1;
-        }
-        const double rfx = lists_on ? vref[i] : 0.0, rfy = lists_on ? vref[Np + i] : 0.0, rfz = lists_on ? vref[2 * Np + i] : 0.0;
+        for (int q = 0; q < 2; ++q) cj[q] = lane + 32 * q < cnt ? p_idx[q] : -1;
+        const double rfx = p_rfx, rfy = p_rfy, rfz = p_rfz;
 #pragma unroll
         for (int q = 0; q < 2; ++q) cold[q] = cj[q] >= 0 ? mat[(size_t)i * MS + cj[q]] : 0.0;
+        if (lists_on) {   // the next step's list (lists only change in a rebuild, which clears p_valid)
+            const int in = ring_i[(int)((step0 + (unsigned)done + 1ULL) & 63ULL)];
+            p_cnt = vcnt[in];
+            p_idx[0] = (int)vidx[(size_t)in * VL_K + lane]; p_idx[1] = (int)vidx[(size_t)in * VL_K + 32 + lane];
+            p_rfx = vref[in]; p_rfy = vref[Np + in]; p_rfz = vref[2 * Np + in];
+            p_valid = true;
+        }
         // ---- trial move (MCINIT :699-712), RotMatrix of the own site
         const double rv = (isang ? s.dhoekmax : s.dposmax) * ring_rv[6 * ring_e + rr];
         const double nv = wrap_fma(base[i] + rv, period, half, inv_half);
@@ -266,7 +283,8 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
         if (done > 0) s.ratio = (double)((float)racc / (float)s.nadj);
         ctl[c] = s;
         if (out_steps) out_steps[c] = done;
-        vcnt[N] = (int)nrebuild;   // diagnostic: list rebuilds in this launch (slot N of the count array)
+        vcnt[N] = (int)nrebuild;   // diagnostic: list rebuilds in this launch
+        vcnt[N + 1] = lists_on && !need_rebuild ? 1 : 0;
     }
 }
 

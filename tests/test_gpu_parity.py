@@ -273,13 +273,12 @@ def test_batched_mode_replica_box(shipped, matrix_mode, lookahead):
 
 @pytest.mark.parametrize("skin", ["0.25", "1.0", None])
 def test_large_box_neighbour_lists(shipped, skin, monkeypatch):
-    """N = 240 runs through k_run_vl (Verlet lists in global memory).  A tiny skin forces the fall-back to the full
+    """N = 240 runs through k_run_vl (Verlet lists in global memory, the default for boxes of this size).  A tiny skin forces the fall-back to the full
     scan and list rebuilds every few accepted moves; the chain must stay the oracle's either way, and equal to the
     list-free kernel's."""
     box, system = shipped
     b = boxio.replicate(box, 2)
     s = _sys_for(system, b)
-    monkeypatch.setenv("MCB200_VERLET_MIN_N", "33")     # by default the lists start at N > 256
     if skin is None:
         monkeypatch.setenv("MCB200_NO_VERLET", "1")
     else:
@@ -299,6 +298,37 @@ def test_large_box_neighbour_lists(shipped, skin, monkeypatch):
         _compare_chain(st, c, o.stats(), com, hoek, o)
     fresh = eng.total_energy()[0]
     assert np.all(np.abs(fresh - st["toteng"]) <= RTOL * np.abs(fresh))
+
+
+def test_neighbour_lists_follow_state_changes(shipped, monkeypatch):
+    """Lists are kept from one launch to the next only while k_run_vl alone has moved molecules: after new coordinates
+    from the host (here: two distant molecules swapped, so their lists are wrong in every entry) the next launch must
+    rebuild them.  The chain after the swap is compared with an oracle started from the swapped state."""
+    box, system = shipped
+    b = boxio.replicate(box, 2)
+    s = _sys_for(system, b)
+    eng = _engine(s, b.n, n_chains=2)
+    eng.set_state(b.com, b.hoek)
+    eng.seed(np.array([31, 32], dtype=np.uint64))
+    eng.run_steps(1500)
+    eng.run_steps(500)                       # second launch: lists trusted
+    com, hoek = eng.get_state()
+    d = np.linalg.norm(com[0] - com[0][0], axis=1)
+    far = int(np.argmax(d))
+    com2, hoek2 = com.copy(), hoek.copy()
+    com2[:, [0, far]] = com2[:, [far, 0]]
+    eng.set_state(com2, hoek2)
+    eng.reset_stats()
+    eng.set_mc_params()                      # step sizes back to the defaults the oracle starts from
+    eng.seed(np.array([41, 42], dtype=np.uint64))
+    eng.run_steps(2500)
+    st = eng.stats()
+    com3, hoek3 = eng.get_state()
+    for c in range(2):
+        o = ol.OracleChain(s, com2[c], hoek2[c])
+        o.total_energy()
+        o.run_steps_rng(2500, ol.rng_seed(41 + c), trace=False)
+        _compare_chain(st, c, o.stats(), com3, hoek3, o)
 
 
 def test_neighbour_lists_default_size(shipped):
