@@ -7,6 +7,7 @@
 #include "../../include/mcb200.h"
 #include "mcb_kernels.cuh"
 #include "mcb_verlet.cuh"
+#include "mcb_cells.cuh"
 
 #include <cmath>
 #include <cstdio>
@@ -26,6 +27,8 @@ struct mcb_handle {
     bool coul = false, can_step = false, dirty = true, energy_only = false;
     double *big_e = nullptr, *big_sol = nullptr, *big_out = nullptr; long long *big_n = nullptr, *big_nout = nullptr;
     long long big_blocks = 0; int big_tiles = 0;
+    CellGrid cells{};       // cell list of the matrix-free energy (mcb_cells.cuh); nc == 0: not in use
+    int ncell = 0;
     VerletBufs vl{};        // neighbour lists of k_run_vl (large boxes); idx == nullptr: not in use
     cudaStream_t stream = nullptr;
     double *images = nullptr, *matg = nullptr, *work = nullptr;
@@ -132,6 +135,7 @@ extern "C" int mcb_destroy(mcb_t *h)
     cudaFree(h->d_ubuf);
     cudaFree(h->vl.idx); cudaFree(h->vl.cnt); cudaFree(h->vl.ref);
     cudaFree(h->big_e); cudaFree(h->big_sol); cudaFree(h->big_out); cudaFree(h->big_n); cudaFree(h->big_nout);
+    cudaFree(h->cells.count); cudaFree(h->cells.cell_of); cudaFree(h->cells.order);
     if (h->pin) cudaFreeHost(h->pin);
     delete h;
     return 0;
@@ -205,6 +209,22 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
         CKC(cudaMalloc(&h->big_sol, sizeof(double) * h->big_tiles));
         CKC(cudaMalloc(&h->big_out, sizeof(double) * 2));
         CKC(cudaMalloc(&h->big_nout, sizeof(long long)));
+        // cells at least one cutoff wide (a hair more, so that the rounding of the binning cannot separate a pair
+        // inside the cutoff by two cells); fewer than 3 per side: the all-pairs kernel stays
+        int ncs = (int)floor(g.boxl2 / (g.cutoff * (1.0 + 1e-9)));
+        if (ncs > CELL_NC_MAX) ncs = CELL_NC_MAX;
+        if (ncs >= 3 && g.cutoff > 0.0 && !getenv("MCB200_NO_CELLS")) {
+            h->cells.nc = ncs;
+            h->cells.scale = (double)ncs / g.boxl2;
+            h->ncell = ncs * ncs * ncs;
+            // one allocation: count[ncell] fill[ncell] flag[1] pad start[ncell + 1]
+            CKC(cudaMalloc(&h->cells.count, sizeof(int) * ((size_t)3 * h->ncell + 4)));
+            h->cells.fill = h->cells.count + h->ncell;
+            h->cells.flag = h->cells.fill + h->ncell;
+            h->cells.start = h->cells.flag + 2;
+            CKC(cudaMalloc(&h->cells.cell_of, sizeof(int) * (size_t)g.N));
+            CKC(cudaMalloc(&h->cells.order, sizeof(int) * (size_t)g.N));
+        }
     }
     // neighbour lists for every box whose pair matrix lives in global memory: with the next step's list fetched one
     // step ahead they win from the smallest such box on (N = 240: 6.0e10 vs 4.75e10 site pairs/s for the full scan,
@@ -370,21 +390,42 @@ static int big_energy(mcb_t *h, int c, double *tot, double *esol, long long *pai
 {
     const Geo &g = h->g;
     double *img = h->images + (size_t)c * g.image_doubles;
-    k_big_sites<<<h->big_tiles, BIG_TILE, 0, h->stream>>>(g, h->rel, img);
-    if (h->coul) {
-        k_big_pairs<true><<<(unsigned)h->big_blocks, BIG_TILE, 0, h->stream>>>(g, img, h->big_tiles, h->big_e, h->big_n);
-        k_big_solute<true><<<h->big_tiles, BIG_TILE, 0, h->stream>>>(g, img, h->big_sol);
-    } else {
-        k_big_pairs<false><<<(unsigned)h->big_blocks, BIG_TILE, 0, h->stream>>>(g, img, h->big_tiles, h->big_e, h->big_n);
-        k_big_solute<false><<<h->big_tiles, BIG_TILE, 0, h->stream>>>(g, img, h->big_sol);
-    }
-    k_big_reduce<<<1, BIG_TILE, 0, h->stream>>>(h->big_e, h->big_n, h->big_blocks, h->big_sol, h->big_tiles, h->big_out, h->big_nout);
-    h->launches += 4;
-    CK(h, cudaGetLastError());
     double out[2]; long long n;
-    CK(h, cudaMemcpyAsync(out, h->big_out, sizeof(out), cudaMemcpyDeviceToHost, h->stream));
-    CK(h, cudaMemcpyAsync(&n, h->big_nout, sizeof(n), cudaMemcpyDeviceToHost, h->stream));
-    CK(h, cudaStreamSynchronize(h->stream));
+    k_big_sites<<<h->big_tiles, BIG_TILE, 0, h->stream>>>(g, h->rel, img);
+    if (h->coul) k_big_solute<true><<<h->big_tiles, BIG_TILE, 0, h->stream>>>(g, img, h->big_sol);
+    else k_big_solute<false><<<h->big_tiles, BIG_TILE, 0, h->stream>>>(g, img, h->big_sol);
+    h->launches += 2;
+    bool need_all_pairs = true;
+    if (h->cells.nc) {
+        // candidates from a cell list; the flag says whether the box allowed it (every centre of mass inside it)
+        const CellGrid &cg = h->cells;
+        CK(h, cudaMemsetAsync(cg.count, 0, sizeof(int) * ((size_t)2 * h->ncell + 2), h->stream));   // count, fill, flag
+        k_cell_assign<<<h->big_tiles, BIG_TILE, 0, h->stream>>>(g, img, cg);
+        k_cell_scan<<<1, 1024, 0, h->stream>>>(cg, h->ncell);
+        k_cell_scatter<<<h->big_tiles, BIG_TILE, 0, h->stream>>>(g, cg);
+        k_cell_sort<<<(h->ncell + BIG_TILE - 1) / BIG_TILE, BIG_TILE, 0, h->stream>>>(cg, h->ncell);
+        if (h->coul) k_cell_pairs<true><<<h->big_tiles, BIG_TILE, 0, h->stream>>>(g, img, cg, h->big_e, h->big_n);
+        else k_cell_pairs<false><<<h->big_tiles, BIG_TILE, 0, h->stream>>>(g, img, cg, h->big_e, h->big_n);
+        k_big_reduce<<<1, BIG_TILE, 0, h->stream>>>(h->big_e, h->big_n, h->big_tiles, h->big_sol, h->big_tiles, h->big_out, h->big_nout);
+        h->launches += 6;
+        CK(h, cudaGetLastError());
+        int flag = 0;
+        CK(h, cudaMemcpyAsync(out, h->big_out, sizeof(out), cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaMemcpyAsync(&n, h->big_nout, sizeof(n), cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaMemcpyAsync(&flag, cg.flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));
+        need_all_pairs = flag != 0;
+    }
+    if (need_all_pairs) {
+        if (h->coul) k_big_pairs<true><<<(unsigned)h->big_blocks, BIG_TILE, 0, h->stream>>>(g, img, h->big_tiles, h->big_e, h->big_n);
+        else k_big_pairs<false><<<(unsigned)h->big_blocks, BIG_TILE, 0, h->stream>>>(g, img, h->big_tiles, h->big_e, h->big_n);
+        k_big_reduce<<<1, BIG_TILE, 0, h->stream>>>(h->big_e, h->big_n, h->big_blocks, h->big_sol, h->big_tiles, h->big_out, h->big_nout);
+        h->launches += 2;
+        CK(h, cudaGetLastError());
+        CK(h, cudaMemcpyAsync(out, h->big_out, sizeof(out), cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaMemcpyAsync(&n, h->big_nout, sizeof(n), cudaMemcpyDeviceToHost, h->stream));
+        CK(h, cudaStreamSynchronize(h->stream));
+    }
     const double t = out[1] + out[0];
     CK(h, cudaMemcpyAsync(reinterpret_cast<char *>(h->ctl + c) + offsetof(ChainCtl, toteng), &t, sizeof(double), cudaMemcpyHostToDevice, h->stream));
     CK(h, cudaStreamSynchronize(h->stream));

@@ -108,6 +108,44 @@ def test_config5_hundred_thousand_molecules(shipped):
         eng.matrix(0)
 
 
+def test_cell_list_against_all_pairs(shipped, monkeypatch):
+    """The matrix-free energy finds its pairs through a cell list (mcb_cells.cuh) when every centre of mass is inside
+    the box, and through the all-pairs kernel otherwise.  Same pairs and the same energy to rounding on a shuffled
+    5x5x5 replica; with one molecule pushed outside the box the cell path must hand over to the all-pairs kernel
+    (bit-identical result), because the reference's minimum image is no longer a metric there."""
+    box, system = shipped
+    b = boxio.replicate(box, 5)
+    s5 = _sys_for(system, b)
+    rng = np.random.default_rng(3)
+    perm = rng.permutation(b.n)                      # cell order != index order
+    com, hoek = b.com[perm].copy(), b.hoek[perm].copy()
+
+    def energy(c, h, cells):
+        if cells:
+            monkeypatch.delenv("MCB200_NO_CELLS", raising=False)
+        else:
+            monkeypatch.setenv("MCB200_NO_CELLS", "1")
+        eng = _engine(s5, b.n, n_chains=1)
+        eng.set_state(c, h)
+        r = eng.total_energy()
+        r2 = eng.total_energy()
+        assert r[0][0] == r2[0][0] and r[2][0] == r2[2][0]      # same bits on a second call
+        return r[0][0], r[1][0], int(r[2][0])
+
+    t_c, es_c, n_c = energy(com, hoek, True)
+    t_a, es_a, n_a = energy(com, hoek, False)
+    assert n_c == n_a and es_c == es_a
+    assert abs(t_c - t_a) <= 1e-12 * abs(t_a)
+    o = ol.OracleChain(s5, com, hoek, keep_matrix=False)
+    e, es, npair = o.total_energy_matrixfree(cells=False)
+    assert n_c == npair and abs(t_c - e) <= RTOL * abs(e)
+    com_out = com.copy()
+    com_out[17, 0] += 2.5 * b.boxl                   # far outside [-BOXL, BOXL]
+    t_c2, _, n_c2 = energy(com_out, hoek, True)
+    t_a2, _, n_a2 = energy(com_out, hoek, False)
+    assert n_c2 == n_a2 and t_c2 == t_a2
+
+
 def test_coulomb_path_when_conv_is_nonzero(shipped):
     """The reference's CONV is 0 (LennardJones.f90:57); the kernel still carries q1 q2 / r * conv."""
     box, system = shipped
