@@ -566,6 +566,9 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
     const unsigned long long step0 = (unsigned long long)s.step;
     const int nsteps_i = (int)min(nsteps, (long long)0x3fffffff);
     unsigned long long gen_end = step0;                             // ring holds steps [.., gen_end)
+    // launch-local index of the first production step: step0 + k + 1 >= start_prod (MonteCarlo.F90:760)
+    const long long pf = s.start_prod - (long long)step0 - 1;
+    const int prod_from = pf <= 0 ? 0 : (pf > 0x3fffffff ? 0x7fffffff : (int)pf);
 #ifdef MCB_PHASE_CLOCKS
     long long ph[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tph = clock64();
 #endif
@@ -633,8 +636,10 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
 #pragma unroll
                 for (int m = 0; m < MCH; ++m) {
                     const int j = 32 * (wb + q) + r + GL * m;
-                    in[q * MCH + m] = false;
-                    if (j < N && j != i) in[q * MCH + m] = !(pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2);
+                    // every lane computes a distance (lanes past N on molecule 0) and the guard selects: no branch in the gate
+                    const int jj = j < N ? j : 0;
+                    const double r2 = pair_r2(com[jj] - ncx, com[Np + jj] - ncy, com[2 * Np + jj] - ncz, g);
+                    in[q * MCH + m] = !((j < N && j != i ? r2 : DBL_HUGE) > g.cut2);
                 }
 #pragma unroll
             for (int q = 0; q < GB; ++q) {
@@ -670,7 +675,8 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
         double dE = lane_tot - old_part;
         double esol = 0.0;
         __syncwarp();
-        for (int p = sub; p < nsolp; p += NSUB) esol += epart[4 * p + a];
+        if (sub < nsolp) esol = epart[4 * sub + a];
+        if (nsolp > NSUB) for (int p = sub + NSUB; p < nsolp; p += NSUB) esol += epart[4 * p + a];   // more than 4*NSUB solute atoms
 #pragma unroll
         for (int o = GL / 2; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
         // METROPOLIS (:720-788) on DELTA = dE
@@ -774,13 +780,14 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
                 nclamp += (x.flags >> 2) & 1;
                 sitepairs += (unsigned)(wpair * x.nn + wsol);
                 s.last_delta = x.dE;
-                const bool in_prod = (long long)(step0 + (unsigned)(done + gg) + 1ULL) >= s.start_prod;
-                if (x.flags & 1) {
-                    nsuc++; nacc++;
-                    s.toteng += x.dE;
-                    if (in_prod) { s.production += s.toteng; prod_acc++; }
-                }
-                if (in_prod) { s.sum_e += s.toteng; s.sum_e2 = fma(s.toteng, s.toteng, s.sum_e2); nstat++; }
+                // selects instead of branches: adding 0.0 leaves the sums as they are
+                const bool in_prod = done + gg >= prod_from;
+                const bool acc = (x.flags & 1) != 0;
+                nsuc += acc; nacc += acc;
+                s.toteng += acc ? x.dE : 0.0;
+                s.production += acc && in_prod ? s.toteng : 0.0; prod_acc += acc && in_prod;
+                const double te = in_prod ? s.toteng : 0.0;
+                s.sum_e += te; s.sum_e2 = fma(te, te, s.sum_e2); nstat += in_prod;
             }
         }
         racc = nacc;
