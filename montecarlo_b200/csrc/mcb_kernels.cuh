@@ -565,7 +565,8 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
     unsigned long long sitepairs = 0;
     const unsigned long long step0 = (unsigned long long)s.step;
     const int nsteps_i = (int)min(nsteps, (long long)0x3fffffff);
-    unsigned long long gen_end = step0;                             // ring holds steps [.., gen_end)
+    int ring_hi = 0;                                                // the ring holds the launch-local steps [ring_hi - 64, ring_hi)
+    const int ring0 = (int)(step0 & 63ULL);
     // launch-local index of the first production step: step0 + k + 1 >= start_prod (MonteCarlo.F90:760)
     const long long pf = s.start_prod - (long long)step0 - 1;
     const int prod_from = pf <= 0 ? 0 : (pf > 0x3fffffff ? 0x7fffffff : (int)pf);
@@ -575,8 +576,8 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
 
     while (done < nsteps_i) {
         // ================= pre-draw the next 32 steps when the ring runs low (one step per lane) =================
-        while (step0 + (unsigned)done + T > gen_end) {
-            const unsigned long long sidx = gen_end + (unsigned)lane;
+        while (done + T > ring_hi) {
+            const unsigned long long sidx = step0 + (unsigned)(ring_hi + lane);
             const int e = (int)(sidx & 63ULL);
             const double u0 = stream_uniform(s.rng_key, 8ULL * sidx);
             int ii = (int)(u0 * (double)N) + 1;                     // MCINIT, MonteCarlo.F90:697-698
@@ -589,11 +590,11 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
             }
             // METROPOLIS draws RV <= E**x; with x < 0 that is log(RV)/log(E) <= x, and the left side needs only the uniform
             ring_thr[e] = log(stream_uniform(s.rng_key, 8ULL * sidx + 7)) * (1.0 / LN_E_F32);
-            gen_end += 32;
+            ring_hi += 32;
             __syncwarp();
         }
         // ================= evaluation of step (done + gidx) by this group =================
-        const int ring_e = (int)((step0 + (unsigned)(done + gidx)) & 63ULL);
+        const int ring_e = (ring0 + done + gidx) & 63;
         const int i = ring_i[ring_e];
         const double thr = ring_thr[ring_e];
         // sum of the old matrix row + ENERGY(i), straight from the running row sums
@@ -668,15 +669,19 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
         const int nslots = nsolp + nn;
         double lane_tot = 0.0;
         constexpr int NI = GL == 32 ? 2 : 4;   // (a shorter tail pass was tried: the extra code paths cost more than they saved)
-        for (int s0 = sub; s0 < nslots; s0 += NI * NSUB)
-            lane_tot += items_staged<COUL, NI>(g, sites, tabAB, tabQ, list, nsolp, nslots, s0, NSUB, a, sx, sy, sz, epart);
+        // (the same number of passes on every lane: a uniform loop, lanes past the last slot evaluate slot 0 and drop it)
+        for (int sb = 0; sb < nslots; sb += NI * NSUB)
+            lane_tot += items_staged<COUL, NI>(g, sites, tabAB, tabQ, list, nsolp, nslots, sb + sub, NSUB, a, sx, sy, sz, epart);
         PH_T(2);
         // dE = sum(new row) - sum(old row) over the group; ENERGY(i) = the solute slots' share of it
         double dE = lane_tot - old_part;
         double esol = 0.0;
         __syncwarp();
         if (sub < nsolp) esol = epart[4 * sub + a];
-        if (nsolp > NSUB) for (int p = sub + NSUB; p < nsolp; p += NSUB) esol += epart[4 * p + a];   // more than 4*NSUB solute atoms
+        if (nsolp > NSUB) {                                        // more than 4*NSUB solute atoms
+#pragma unroll 1
+            for (int p = sub + NSUB; p < nsolp; p += NSUB) esol += epart[4 * p + a];
+        }
 #pragma unroll
         for (int o = GL / 2; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
         // METROPOLIS (:720-788) on DELTA = dE
@@ -754,11 +759,14 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
                     }
                 }
                 // partners inside the cutoff: SS(i,j) = SS(j,i) = EN (:819-820), row sums follow
+                // (at most 31 partners in a SMALL box: one partner per lane, no loop)
                 for (int sl = nsolp + r; sl < nslots; sl += GL) {
                     const int j = list[sl];
-                    const double e = (epart[4 * sl] + epart[4 * sl + 1]) + (epart[4 * sl + 2] + epart[4 * sl + 3]);
+                    const double2 e01 = *reinterpret_cast<const double2 *>(epart + 4 * sl), e23 = *reinterpret_cast<const double2 *>(epart + 4 * sl + 2);
+                    const double e = (e01.x + e01.y) + (e23.x + e23.y);
                     rowsum[j] += e - mat[(size_t)i * MS + j];
                     mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
+                    if (SMALL && GL == 32) break;
                 }
                 if (r >= 1 && r <= 6) base[i] = nv;
                 if (r < 4) {
