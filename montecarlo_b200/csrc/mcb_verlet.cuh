@@ -96,6 +96,8 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
     const unsigned long long step0 = (unsigned long long)s.step;
     const int nsteps_i = (int)min(nsteps, (long long)0x3fffffff);
     unsigned long long gen_end = step0;
+    const long long pf = s.start_prod - (long long)step0 - 1;     // launch-local index of the first production step (:760)
+    const int prod_from = pf <= 0 ? 0 : (pf > 0x3fffffff ? 0x7fffffff : (int)pf);
     // list of the NEXT step's molecule (known from the ring), fetched one step ahead: count, candidates, build position
     int p_cnt = -1, p_idx[2] = {0, 0};
     double p_rfx = 0.0, p_rfy = 0.0, p_rfz = 0.0;
@@ -183,8 +185,11 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
         bool cin[2] = {false, false};
         if (use_list) {
 #pragma unroll
-            for (int q = 0; q < 2; ++q)
-                if (cj[q] >= 0) cin[q] = !(pair_r2(com[cj[q]] - ncx, com[Np + cj[q]] - ncy, com[2 * Np + cj[q]] - ncz, g) > g.cut2);
+            for (int q = 0; q < 2; ++q) {   // every lane computes a distance (empty lanes on molecule 0), the guard selects
+                const int jj = cj[q] >= 0 ? cj[q] : 0;
+                const double r2 = pair_r2(com[jj] - ncx, com[Np + jj] - ncy, com[2 * Np + jj] - ncz, g);
+                cin[q] = !((cj[q] >= 0 ? r2 : DBL_HUGE) > g.cut2);
+            }
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
                 const unsigned b = __ballot_sync(FULL, cin[q]);
@@ -204,11 +209,15 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
         // ---- site pairs (calcLJ / CalcLJ_SV), staged
         const int nslots = nsolp + nn;
         double lane_tot = 0.0;
-        for (int s0 = sub; s0 < nslots; s0 += 2 * 8)
-            lane_tot += items_staged<COUL, 2>(g, sites, tabAB, tabQ, list, nsolp, nslots, s0, 8, a, sx, sy, sz, epart);
+        for (int sb = 0; sb < nslots; sb += 2 * 8)   // the same number of passes on every lane
+            lane_tot += items_staged<COUL, 2>(g, sites, tabAB, tabQ, list, nsolp, nslots, sb + sub, 8, a, sx, sy, sz, epart);
         double dE = lane_tot - old_part, esol = 0.0;
         __syncwarp();
-        for (int p = sub; p < nsolp; p += 8) esol += epart[4 * p + a];
+        if (sub < nsolp) esol = epart[4 * sub + a];
+        if (nsolp > 8) {
+#pragma unroll 1
+            for (int p = sub + 8; p < nsolp; p += 8) esol += epart[4 * p + a];
+        }
 #pragma unroll
         for (int o = 16; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
         // ---- METROPOLIS (:720-788) on DELTA = dE
@@ -254,13 +263,12 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
         nclamp += clamped ? 1 : 0;
         sitepairs += (unsigned)(wpair * nn + wsol);
         s.last_delta = dE;
-        const bool in_prod = (long long)(step0 + (unsigned)done + 1ULL) >= s.start_prod;
-        if (accept) {
-            nsuc++; nacc++;
-            s.toteng += dE;
-            if (in_prod) { s.production += s.toteng; prod_acc++; }
-        }
-        if (in_prod) { s.sum_e += s.toteng; s.sum_e2 = fma(s.toteng, s.toteng, s.sum_e2); nstat++; }
+        const bool in_prod = done >= prod_from;                    // selects instead of branches: adding 0.0 changes nothing
+        nsuc += accept; nacc += accept;
+        s.toteng += accept ? dE : 0.0;
+        s.production += accept && in_prod ? s.toteng : 0.0; prod_acc += accept && in_prod;
+        const double te = in_prod ? s.toteng : 0.0;
+        s.sum_e += te; s.sum_e2 = fma(te, te, s.sum_e2); nstat += in_prod;
         racc = nacc;
         if (++adj_count == s.nadj) {                                // mod(I, NADJ) == 0, :766-777
             adj_count = 0;
