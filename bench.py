@@ -330,7 +330,7 @@ def run_gpu_arm(args):
             "clocks": clocks,
             "roofline": {"bound": "fp64", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
                          "frac": achieved_tf / peak_tf, "traffic": traffic,
-                         "kernel": "k_run_steps", "flop_per_site_pair": FLOP_PER_SITEPAIR,
+                         "kernel": "k_run_spec", "flop_per_site_pair": FLOP_PER_SITEPAIR,
                          "site_pairs_per_launch": w_launch, "kernel_ms": 1e3 * t_launch,
                          "peak_source": "measured live: mcb_measure_fp64_peak (independent DFMA chains, all SMs); "
                                         "MEASURED_PEAKS.json has no fp64 entry",
