@@ -359,10 +359,19 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--lookahead", type=int, default=0, help="speculative look-ahead depth of mcb_run_steps (0 = library default)")
     args = ap.parse_args()
-    if args.impl == "reference":
-        run_reference_arm(args)
-    else:
-        run_gpu_arm(args)
+    # stdout carries the ONE JSON line and nothing else: libraries that write to file descriptor 1 (NCCL prints a
+    # version banner there when NCCL_DEBUG asks for it) are sent to stderr for the duration of the run
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w")
+    try:
+        if args.impl == "reference":
+            run_reference_arm(args)
+        else:
+            run_gpu_arm(args)
+    finally:
+        sys.stdout.flush()
 
 
 if __name__ == "__main__":
