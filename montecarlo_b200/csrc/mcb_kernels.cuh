@@ -682,6 +682,22 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
 #pragma unroll 1
             for (int p = sub + NSUB; p < nsolp; p += NSUB) esol += epart[4 * p + a];
         }
+        // One step per warp in a SMALL box: what an accepted move would write (new matrix entries and row sums of
+        // the partners inside the cutoff, the row sums of those that left) does not depend on dE, so it is formed
+        // here, in the shadow of the reduction's shuffles; the commit below is then only stores.
+        constexpr bool HOIST = SMALL && GL == 32 && T == 1;
+        const int c_sl = nsolp + r;
+        const bool c_has = HOIST && c_sl < nslots, c_left = HOIST && oldrow[0] != 0.0 && !((neww0 >> r) & 1u);
+        int c_j = 0;
+        double c_e = 0.0, c_rs_in = 0.0, c_rs_left = 0.0;
+        if (HOIST) {
+            c_j = c_has ? list[c_sl] : 0;
+            const int esl = c_has ? c_sl : 0;
+            const double2 e01 = *reinterpret_cast<const double2 *>(epart + 4 * esl), e23 = *reinterpret_cast<const double2 *>(epart + 4 * esl + 2);
+            c_e = (e01.x + e01.y) + (e23.x + e23.y);
+            c_rs_in = rowsum[c_j] + (c_e - mat[(size_t)i * MS + c_j]);
+            c_rs_left = rowsum[r < N ? r : 0] - oldrow[0];
+        }
 #pragma unroll
         for (int o = GL / 2; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
         // METROPOLIS (:720-788) on DELTA = dE
@@ -727,7 +743,18 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
         // several steps in flight the commits run one after the other.
 #pragma unroll
         for (int cg = 0; cg < T; ++cg) {
-            if (gidx == cg && gidx < progress && accept) {
+            if (HOIST) {
+                if (accept) {
+                    if (c_left) { rowsum[r] = c_rs_left; mat[(size_t)i * MS + r] = 0.0; mat[(size_t)r * MS + i] = 0.0; }
+                    if (c_has) { rowsum[c_j] = c_rs_in; mat[(size_t)i * MS + c_j] = c_e; mat[(size_t)c_j * MS + i] = c_e; }
+                    if (r >= 1 && r <= 6) base[i] = nv;
+                    if (r < 4) {
+                        sites[SITE_DOUBLES * i + 3 * a] = sx; sites[SITE_DOUBLES * i + 3 * a + 1] = sy;
+                        sites[SITE_DOUBLES * i + 3 * a + 2] = sz;
+                    }
+                    if (r == 0) { energy[i] = esol; rowsum[i] = (dE + old_tot) - esol; }   // new row sum = new total - ENERGY(i)
+                }
+            } else if (gidx == cg && gidx < progress && accept) {
                 // partners that left the cutoff: entry to zero, their row sums lose the old pair energy
                 if (prefetched) {
 #pragma unroll
