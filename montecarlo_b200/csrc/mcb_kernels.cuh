@@ -738,6 +738,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
                 }
             }
         }
+        PH_T(5);
         // ================= commit the accepted steps that stand =================
         // They are mutually independent, but two of them can share a neighbour whose row sum both adjust, so with
         // several steps in flight the commits run one after the other.
@@ -804,6 +805,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
             }
             if (T > 1) { if (W > 1) __syncthreads(); else __syncwarp(); }
         }
+        PH_T(6);
         // ================= bookkeeping in step order (every warp keeps the same copy) =================
 #pragma unroll
         for (int gg = 0; gg < T; ++gg) {

@@ -33,9 +33,9 @@ buf = (C.c_ulonglong * 8)()
 lib.mcb_debug_phase_clocks(buf, 1)
 eng.run_steps(S)
 lib.mcb_debug_phase_clocks(buf, 0)
-names = ["mcinit (rng, old row, move, sincos, rotate)", "centre-of-mass gate + list", "site-pair items", "reduce + metropolis", "resolve + commit + bookkeeping"]
-tot = sum(buf[:5])
-for n, v in zip(names, buf[:5]):
+names = ["mcinit (rng, old row, move, sincos, rotate)", "centre-of-mass gate + list", "site-pair items", "reduce + metropolis", "bookkeeping", "exchange + resolution", "commit"]
+tot = sum(buf[:7])
+for n, v in zip(names, buf[:7]):
     print(f"{n:32s} {v / (nch * S):9.1f} cyc/step  {100.0 * v / tot:5.1f}%")
 import os
 print(f"{'total':32s} {tot / (nch * S):9.1f} cyc/step (per committed step, lookahead={la}, tune={os.environ.get('MCB200_TUNE')})")
