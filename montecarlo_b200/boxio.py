@@ -97,6 +97,106 @@ def write_box(box: Box, path: str | Path) -> None:
     Path(path).write_text("\n".join(out) + "\n")
 
 
+def _records(buf: bytes):
+    """Fortran sequential unformatted records: 4-byte length, payload, the same length again."""
+    p = 0
+    while p < len(buf):
+        n = int.from_bytes(buf[p:p + 4], "little")
+        rec = buf[p + 4:p + 4 + n]
+        if int.from_bytes(buf[p + 4 + n:p + 8 + n], "little") != n:
+            raise ValueError("not a sequential unformatted file (record markers disagree)")
+        yield rec
+        p += n + 8
+
+
+def read_box_bin(path: str | Path) -> Box:
+    """Reads the unformatted box (reference MC_lib/lib_read.f90:117-175 READ_BIN; records in SURVEY.md appendix A):
+    BOXL, nCoM, ENG, BOX_ID(255), N x 6 doubles, "SOLUTE", nSol, SOLNAME(255), nSol x (CHAR*4 + 3 doubles), E_sol,
+    NDIHOEK, NDIHOEK x (2 integers + double; a rotation of 0 means "use the global one" and is stored as -1)."""
+    rec = _records(Path(path).read_bytes())
+    f8 = lambda r: np.frombuffer(r, dtype="<f8")
+    i4 = lambda r: int(np.frombuffer(r[:4], dtype="<i4")[0])
+    boxl = float(f8(next(rec))[0]); n = i4(next(rec)); energy = float(f8(next(rec))[0])
+    box_id = next(rec).decode("latin-1").rstrip()
+    vals = np.array([f8(next(rec))[:6] for _ in range(n)], dtype=np.float64).reshape(n, 6)
+    box = Box(boxl=boxl, com=vals[:, 0:3].copy(), hoek=vals[:, 3:6].copy(), energy=energy, box_id=box_id)
+    if next(rec).decode("latin-1").strip().upper() != "SOLUTE":
+        raise ValueError("SOLUTE record expected")
+    nsol = i4(next(rec))
+    box.sol_name = next(rec).decode("latin-1").rstrip()
+    syms, xyz = [], []
+    for _ in range(nsol):
+        r = next(rec)
+        syms.append(r[:4].decode("latin-1").strip()); xyz.append(f8(r[4:28]))
+    box.sol_sym, box.solute = syms, np.array(xyz, dtype=np.float64).reshape(nsol, 3)
+    box.e_sol = float(f8(next(rec))[0])
+    for _ in range(i4(next(rec))):
+        r = next(rec)
+        a, b = np.frombuffer(r[:8], dtype="<i4")
+        rot = float(f8(r[8:16])[0])
+        box.dihedrals.append((int(a), int(b), -1.0 if rot == 0.0 else rot))
+    return box
+
+
+def write_box_bin(box: Box, path: str | Path) -> None:
+    """Writes the unformatted box READ_BIN accepts (reference MC_lib/lib_read.f90:177-225 WRITE_BIN)."""
+    out = bytearray()
+
+    def put(payload: bytes):
+        n = len(payload).to_bytes(4, "little")
+        out.extend(n); out.extend(payload); out.extend(n)
+
+    f8 = lambda *v: np.asarray(v, dtype="<f8").tobytes()
+    i4 = lambda *v: np.asarray(v, dtype="<i4").tobytes()
+    put(f8(box.boxl)); put(i4(box.n)); put(f8(box.energy))
+    put(box.box_id.encode("latin-1")[:255].ljust(255))
+    for c, h in zip(box.com, box.hoek):
+        put(f8(*c, *h))
+    put(b"SOLUTE"); put(i4(box.nsol))
+    put(box.sol_name.encode("latin-1")[:255].ljust(255))
+    for sym, x in zip(box.sol_sym, box.solute):
+        put(sym.encode("latin-1")[:4].ljust(4) + f8(*x))
+    put(f8(box.e_sol)); put(i4(len(box.dihedrals)))
+    for a, b, r in box.dihedrals:
+        put(i4(a, b) + f8(r))
+    Path(path).write_bytes(bytes(out))
+
+
+def check_box(box: Box) -> dict:
+    """The checks ChecknPrep runs on a box before a run (reference ChecknPrep/check.f90:130-229), on an already parsed
+    box: returns {"errors": [...], "warnings": [...], "info": [...]}.  The reference counts a warning for BOXL, nCoM,
+    the box energy, nSol or E_sol equal to 0 and for every molecule line with a coordinate or angle exactly 0, and an
+    error for a dihedral bond that names atom 0 or an atom beyond nSol; "NDIHOEK is 0" is tested on nCoM there
+    (check.f90:205-208), which is kept.  One note of our own: a centre of mass outside [-BOXL, BOXL] is legal for the
+    reference but switches this library's neighbour and cell lists off (csrc/mcb_verlet.cuh, csrc/mcb_cells.cuh)."""
+    err, war, info = [], [], []
+    if box.boxl == 0.0:
+        war.append("BOXL is 0!")
+    if box.n == 0:
+        war.append("nCoM is 0!")
+    if box.energy == ENERGY_ABSENT:
+        info.append("No energy detected in input box.")
+    if box.energy == 0.0:
+        war.append("ENG is 0!")
+    for i, (c, h) in enumerate(zip(box.com, box.hoek)):
+        if np.any(np.asarray(c) == 0.0) or np.any(np.asarray(h) == 0.0):
+            war.append(f"coordinates are 0! Molecule: {i + 1}")
+    if box.nsol == 0:
+        war.append("nSOL is 0!")
+    if box.e_sol == 0.0:
+        war.append("E_SOL is 0!")
+    if box.n == 0:
+        war.append("NDHIHOEK is 0!")
+    for k, (a, b, rot) in enumerate(box.dihedrals):
+        if rot == 0.0 or rot == -1.0:
+            info.append(f"MaxRot is not defined at dihedral {k + 1}")
+        if a > box.nsol or b > box.nsol or a == 0 or b == 0:
+            err.append(f"Values are out of bounds! Dihedral {k + 1}: {a:03d} {b:03d} {rot:8.2f}")
+    if box.n and box.boxl > 0.0 and np.any(np.abs(box.com) > box.boxl):
+        info.append("a centre of mass lies outside [-BOXL, BOXL]: neighbour and cell lists stay off for this box")
+    return {"errors": err, "warnings": war, "info": info}
+
+
 def box_text(box: Box) -> str:
     import io, tempfile, os
     fd, name = tempfile.mkstemp(suffix=".box")

@@ -1,5 +1,8 @@
 """CPU: the driver's file formats and the box generators (host logic, no energies)."""
+from pathlib import Path
+
 import numpy as np
+import pytest
 
 import oracle_lib as ol
 from montecarlo_b200 import boxio
@@ -48,3 +51,42 @@ def test_replicate_and_scale(shipped):
     assert b3.n == 810 and np.array_equal(b3.solute, box.solute)
     s = boxio.scale(box, 0.9)
     assert s.n == 30 and s.boxl == box.boxl * 0.9 and np.array_equal(s.com, box.com * 0.9)
+
+
+def test_unformatted_box_is_the_text_box(tmp_path, shipped):
+    """The reference ships the same box as text and as a Fortran sequential unformatted file (boxbin/box.txt,
+    boxbin/box.bin, converted by boxbin/boxbin.f90 with MC_lib/lib_read.f90 READ_BIN / WRITE_BIN): every number must be
+    the same through both readers, and writing the binary box again must give the reference's file byte for byte."""
+    box, _ = shipped
+    golden = Path(__file__).parent / "golden" / "inputs" / "box.bin"
+    b = boxio.read_box_bin(golden)
+    assert b.boxl == box.boxl and b.n == box.n and b.energy == box.energy
+    assert np.array_equal(b.com, box.com) and np.array_equal(b.hoek, box.hoek)
+    assert b.sol_sym == box.sol_sym and np.array_equal(b.solute, box.solute) and b.sol_name == box.sol_name
+    assert b.e_sol == box.e_sol and b.dihedrals == box.dihedrals
+    out = tmp_path / "out.bin"
+    boxio.write_box_bin(b, out)
+    assert out.read_bytes() == golden.read_bytes()
+    # a rotation of 0 is stored as "use the global one" (lib_read.f90:168)
+    b0 = boxio.Box(**{**b.__dict__, "dihedrals": [(8, 1, 0.0)]})
+    boxio.write_box_bin(b0, out)
+    assert boxio.read_box_bin(out).dihedrals == [(8, 1, -1.0)]
+    with pytest.raises(ValueError):
+        boxio.read_box_bin(Path(__file__).parent / "golden" / "inputs" / "box.txt")
+
+
+def test_check_box_follows_checknprep(shipped):
+    """ChecknPrep's box checks (check.f90:130-229): the shipped box is clean; zeros, an empty solute and a dihedral
+    bond beyond nSol are reported the way the reference counts them."""
+    box, _ = shipped
+    r = boxio.check_box(box)
+    assert r == {"errors": [], "warnings": [], "info": []}
+    com = box.com.copy(); com[4, 1] = 0.0
+    bad = boxio.Box(**{**box.__dict__, "com": com, "energy": 0.0, "e_sol": 0.0, "dihedrals": [(8, 1, 0.0), (12, 1, 30.0), (0, 3, 30.0)]})
+    r = boxio.check_box(bad)
+    assert r["warnings"] == ["ENG is 0!", "coordinates are 0! Molecule: 5", "E_SOL is 0!"]
+    assert len(r["errors"]) == 2 and "Dihedral 2: 012 001" in r["errors"][0] and "Dihedral 3: 000 003" in r["errors"][1]
+    assert r["info"] == ["MaxRot is not defined at dihedral 1"]
+    far = box.com.copy(); far[0, 0] = 3.0 * box.boxl
+    r = boxio.check_box(boxio.Box(**{**box.__dict__, "com": far, "energy": boxio.ENERGY_ABSENT}))
+    assert r["info"][0] == "No energy detected in input box." and "outside" in r["info"][1]
