@@ -387,6 +387,40 @@ def test_neighbour_lists_default_size(shipped):
         _compare_chain(st, c, o.stats(), com, hoek, o)
 
 
+@pytest.mark.parametrize("k", [1, 2])
+def test_large_solute(shipped, k):
+    """A solute of 37 atoms: 10 pseudo-molecules of four sites (the last one padded), i.e. more solute slots than one
+    pass over the partner slots holds, in the small box (k_run_spec) and in the 2x2x2 replica (k_run_vl); start-up
+    energy, single-step mode and 1500 batched steps against the oracle."""
+    box, system = shipped
+    b = boxio.replicate(box, k) if k > 1 else box
+    base = _sys_for(system, b) if k > 1 else system
+    rng = np.random.default_rng(37)
+    reps = [base.solute] + [base.solute + rng.uniform(-0.8, 0.8, size=(1, 3)) + 0.3 * rng.standard_normal(base.solute.shape) for _ in range(3)]
+    sol = np.concatenate(reps)[:37]
+    tab = np.concatenate([base.sol_tab] * 4)[:37]
+    syms = (base.sol_sym * 4)[:37]
+    s = boxio.System(**{**base.__dict__, "solute": sol, "sol_tab": tab, "sol_sym": syms})
+    nch = 2
+    eng = _engine(s, b.n, n_chains=nch)
+    eng.set_state(b.com, b.hoek)
+    tot, esol, _ = eng.total_energy()
+    o0 = ol.OracleChain(s, b.com, b.hoek)
+    e0 = o0.total_energy()
+    assert abs(tot[0] - e0) <= RTOL * abs(e0)
+    eng.seed(np.array([71, 72], dtype=np.uint64))
+    eng.run_steps(1500)
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    for c in range(nch):
+        o = ol.OracleChain(s, b.com, b.hoek)
+        o.total_energy()
+        o.run_steps_rng(1500, ol.rng_seed(71 + c), trace=False)
+        _compare_chain(st, c, o.stats(), com, hoek, o)
+    fresh = eng.total_energy()[0]
+    assert np.all(np.abs(fresh - st["toteng"]) <= RTOL * np.abs(fresh))
+
+
 def test_per_chain_solute_conformers(shipped):
     """Config 4 shape: every chain sees its own solute coordinates."""
     box, system = shipped
