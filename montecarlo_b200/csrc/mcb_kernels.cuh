@@ -561,8 +561,8 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
     const int ga = lane - gb * (gb - 1) / 2;
     int adj_count = (int)(s.step % s.nadj);
     int done = 0;
-    unsigned nsuc = 0, nacc = (unsigned)s.naccept, racc = 0, nclamp = 0, uused = 0, prod_acc = 0, nstat = 0;
-    unsigned long long sitepairs = 0;
+    unsigned nsuc = 0, nacc = (unsigned)s.naccept, racc = 0, nclamp = 0, n_used8 = 0, prod_acc = 0;
+    unsigned long long sum_nn = 0;
     const unsigned long long step0 = (unsigned long long)s.step;
     const int nsteps_i = (int)min(nsteps, (long long)0x3fffffff);
     int ring_hi = 0;                                                // the ring holds the launch-local steps [ring_hi - 64, ring_hi)
@@ -813,9 +813,10 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
                 SpecX x;
                 if (T > 1) x = xch[gg];
                 else { x.dE = dE; x.nn = nn; x.flags = (accept ? 1 : 0) | (used8 ? 2 : 0) | (clamped ? 4 : 0); }   // one step in flight: no exchange
-                uused += 7 + ((x.flags >> 1) & 1);
+                // (uniforms used, site pairs and production samples follow from these sums and the step count at the end)
+                n_used8 += (x.flags >> 1) & 1;
                 nclamp += (x.flags >> 2) & 1;
-                sitepairs += (unsigned)(wpair * x.nn + wsol);
+                sum_nn += (unsigned)x.nn;
                 s.last_delta = x.dE;
                 // selects instead of branches: adding 0.0 leaves the sums as they are
                 const bool in_prod = done + gg >= prod_from;
@@ -824,7 +825,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
                 s.toteng += acc ? x.dE : 0.0;
                 s.production += acc && in_prod ? s.toteng : 0.0; prod_acc += acc && in_prod;
                 const double te = in_prod ? s.toteng : 0.0;
-                s.sum_e += te; s.sum_e2 = fma(te, te, s.sum_e2); nstat += in_prod;
+                s.sum_e += te; s.sum_e2 = fma(te, te, s.sum_e2);
             }
         }
         racc = nacc;
@@ -850,8 +851,10 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
         if (MAT_SMEM) for (int qq = tid; qq < N * MS; qq += 32 * W) gimg[g.o_mat + qq] = img[g.o_mat + qq];
     }
     if (tid == 0) {
-        s.step += done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.uused += uused; s.prod_acc += prod_acc;
-        s.nstat += nstat; s.sitepairs += (long long)sitepairs;
+        s.step += done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.prod_acc += prod_acc;
+        s.uused += 7LL * done + n_used8;                                      // 7 uniforms per step, an 8th when METROPOLIS draws
+        s.nstat += done > prod_from ? done - prod_from : 0;                   // steps at or after start_prod
+        s.sitepairs += (long long)wpair * (long long)sum_nn + (long long)wsol * done;
         if (done > 0) s.ratio = (double)((float)racc / (float)s.nadj);
         ctl[c] = s;
         if (out_steps) out_steps[c] = done;
