@@ -183,6 +183,7 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
         // ---- centre-of-mass gate (:804-813) on the candidates, or on everybody
         int nn = 0;
         bool cin[2] = {false, false};
+        int cslot[2] = {0, 0};
         if (use_list) {
 #pragma unroll
             for (int q = 0; q < 2; ++q) {   // every lane computes a distance (empty lanes on molecule 0), the guard selects
@@ -193,7 +194,8 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
 #pragma unroll
             for (int q = 0; q < 2; ++q) {
                 const unsigned b = __ballot_sync(FULL, cin[q]);
-                if (cin[q]) list[nsolp + nn + __popc(b & lt)] = cj[q];
+                cslot[q] = nsolp + nn + __popc(b & lt);
+                if (cin[q]) list[cslot[q]] = cj[q];
                 nn += __popc(b);
             }
         } else {
@@ -213,6 +215,21 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
             lane_tot += items_staged<COUL, 2>(g, sites, tabAB, tabQ, list, nsolp, nslots, sb + sub, 8, a, sx, sy, sz, epart);
         double dE = lane_tot - old_part, esol = 0.0;
         __syncwarp();
+        // what an accepted move would write for this lane's candidates (new matrix entry: the pair energy inside the
+        // cutoff, 0 outside; the candidate's row sum) does not depend on dE: formed here, in the shadow of the
+        // reduction, from the old entries fetched at the top of the step - the commit is then stores only
+        double cval[2] = {0.0, 0.0}, crs[2] = {0.0, 0.0};
+        bool cchg[2] = {false, false};
+        if (use_list) {
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const int sl = cin[q] ? cslot[q] : 0, jj = cj[q] >= 0 ? cj[q] : 0;
+                const double2 e01 = *reinterpret_cast<const double2 *>(epart + 4 * sl), e23 = *reinterpret_cast<const double2 *>(epart + 4 * sl + 2);
+                cval[q] = cin[q] ? (e01.x + e01.y) + (e23.x + e23.y) : 0.0;
+                crs[q] = rowsum[jj] + (cval[q] - cold[q]);
+                cchg[q] = cj[q] >= 0 && (cin[q] || cold[q] != 0.0);
+            }
+        }
         if (sub < nsolp) esol = epart[4 * sub + a];
         if (nsolp > 8) {
 #pragma unroll 1
@@ -226,16 +243,16 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
         const bool used8 = !clamped && exponent >= -75.0 && exponent < 0.0;
         const bool accept = !clamped && (exponent >= 0.0 || (used8 && thr <= exponent));
         if (accept) {
-            // partners that left the cutoff: entry to zero, their row sums lose the old pair energy
             if (use_list) {
 #pragma unroll
                 for (int q = 0; q < 2; ++q)
-                    if (cold[q] != 0.0 && !cin[q]) {
+                    if (cchg[q]) {   // SS(i,j) = SS(j,i) = EN inside the cutoff (:819-820), 0 for a partner that left it
                         const int j = cj[q];
-                        rowsum[j] -= cold[q];
-                        mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0;
+                        rowsum[j] = crs[q];
+                        mat[(size_t)i * MS + j] = cval[q]; mat[(size_t)j * MS + i] = cval[q];
                     }
             } else {
+                // full scan: partners that left the cutoff, then the partners inside it
                 for (int j = lane; j < N; j += 32) {
                     const double old = mat[(size_t)i * MS + j];
                     if (old != 0.0 && j != i && pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2) {
@@ -243,13 +260,12 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
                         mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0;
                     }
                 }
-            }
-            // partners inside the cutoff: SS(i,j) = SS(j,i) = EN (:819-820), row sums follow
-            for (int sl = nsolp + lane; sl < nslots; sl += 32) {
-                const int j = list[sl];
-                const double e = (epart[4 * sl] + epart[4 * sl + 1]) + (epart[4 * sl + 2] + epart[4 * sl + 3]);
-                rowsum[j] += e - mat[(size_t)i * MS + j];
-                mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
+                for (int sl = nsolp + lane; sl < nslots; sl += 32) {
+                    const int j = list[sl];
+                    const double e = (epart[4 * sl] + epart[4 * sl + 1]) + (epart[4 * sl + 2] + epart[4 * sl + 3]);
+                    rowsum[j] += e - mat[(size_t)i * MS + j];
+                    mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
+                }
             }
             if (lane >= 1 && lane <= 6) base[i] = nv;
             if (lane < 4) {
