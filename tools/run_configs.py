@@ -1,0 +1,109 @@
+"""BASELINE configs[2] and configs[3] at full size, one process per GPU (torchrun), NCCL only at the end.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29512 \
+        tools/run_configs.py --config 3 --steps 20000
+
+  --config 3  2x2x2 replica of the shipped box (N = 240), 4096 chains sharded in contiguous blocks
+  --config 4  dihedral sweep: 36 conformers (0..350 degrees about atoms 9-8-1-2) x 256 chains = 9216 chains; per-chain
+              mean energies are all-gathered, averaged per angle, and handed to the reference's window hopping
+              (postprocess.window_hopping, PostProcess.F90:260-304)
+
+Timing: CUDA events on each rank, maximum over ranks.  Rank 0 prints one JSON line.
+"""
+import argparse
+import json
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from montecarlo_b200 import boxio, dihedral, partition, postprocess  # noqa: E402
+from montecarlo_b200.engine import LJEngine  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--config", type=int, choices=[3, 4], required=True)
+    ap.add_argument("--steps", type=int, default=20000, help="Metropolis steps per chain")
+    ap.add_argument("--launch", type=int, default=5000, help="steps per launch")
+    ap.add_argument("--chains", type=int, default=0, help="total chains (default: 4096 for config 3, 9216 for config 4)")
+    args = ap.parse_args()
+    rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    inputs = ROOT / "tests" / "golden" / "inputs"
+    box = boxio.read_box(inputs / "box.txt")
+    system = boxio.load_system(box, inputs / "DMSO.txt", inputs / "param.txt", inputs / "par_solute.txt")
+    angles = np.arange(0.0, 360.0, 10.0)
+    if args.config == 3:
+        b = boxio.replicate(box, 2)
+        system = boxio.System(**{**system.__dict__, "boxl": b.boxl, "solute": b.solute})
+        n_total = args.chains or 4096
+    else:
+        b = box
+        n_total = args.chains or len(angles) * 256
+    per_angle = n_total // len(angles)
+    start, count = partition.chain_block(rank, world, n_total)
+    eng = LJEngine(system, b.n, n_chains=count, device=local)
+    stream = torch.cuda.current_stream()
+    eng.set_stream(stream.cuda_stream)
+    if args.config == 4:
+        conf, _ = dihedral.conformer_sweep(box.solute, box.sol_sym, box.dihedrals[0][:2], angles)
+        mine = (np.arange(start, start + count) // per_angle).clip(max=len(angles) - 1)   # chain -> angle, contiguous blocks
+        eng.set_solute(conf[mine], np.broadcast_to(system.sol_tab, (count,) + system.sol_tab.shape).copy())
+    eng.set_state(b.com, b.hoek)
+    eng.set_mc_params(start_prod=args.steps // 2)
+    eng.seed(partition.global_seeds(rank, world, n_total))
+    e_start = eng.total_energy()[0]
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record(stream)
+    left = args.steps
+    while left > 0:
+        n = min(left, args.launch)
+        eng.run_steps(n, want_counts=False)
+        left -= n
+    t1.record(stream)
+    torch.cuda.synchronize()
+    ms = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    st = eng.stats()
+    c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    c0.record()
+    tot = partition.reduce_stats(st, device="cuda")                               # the one all-reduce
+    mean_e = partition.gather_per_chain(st["sum_e"] / np.maximum(st["n_stat"], 1), n_total, device="cuda")   # the one all-gather
+    c1.record(); torch.cuda.synchronize()
+    if rank == 0:
+        sec = ms.item() * 1e-3
+        line = {"config": args.config, "n_gpus": world, "n_molecules": b.n, "chains": n_total, "steps_per_chain": args.steps,
+                "seconds": sec, "site_pairs_per_s": tot["sitepairs"] / sec, "trial_moves_per_s": tot["step"] / sec,
+                "acceptance": tot["acceptance"], "mean_production_energy": tot["mean_e"], "start_energy_chain0": float(e_start[0]),
+                "collectives_ms": c0.elapsed_time(c1)}
+        if args.config == 4:
+            per = mean_e[: per_angle * len(angles)].reshape(len(angles), per_angle)
+            e_angle = per.mean(axis=1)
+            line["per_angle_mean_energy"] = [round(float(v), 4) for v in e_angle]
+            line["per_angle_sem"] = [round(float(v), 4) for v in per.std(axis=1) / np.sqrt(per_angle)]
+            # window hopping over the gathered energies: one "run" per chain index inside an angle block
+            rng = np.random.default_rng(2026)
+            old, now, acc = postprocess.window_hopping(per.T.copy(), 300.0, iter(rng.random(4 * per_angle)))
+            visits = np.bincount(np.where(acc, now, old), minlength=len(angles))
+            line["window_hopping"] = {"runs": int(per_angle), "accepted": int(acc.sum()), "most_visited_angle_deg": float(angles[int(np.argmax(visits))])}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
