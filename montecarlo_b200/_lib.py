@@ -14,7 +14,7 @@ PKG = Path(__file__).resolve().parent
 ROOT = PKG.parent
 LIB_PATH = Path(os.environ.get("MCB200_LIB", PKG / "libmcb200.so"))  # override: debug builds only
 SOURCES = [PKG / "csrc" / "mcb200.cu"]
-HEADERS = [PKG / "csrc" / "mcb_device.cuh", PKG / "csrc" / "mcb_kernels.cuh", PKG / "csrc" / "mcb_verlet.cuh", PKG / "csrc" / "mcb_cells.cuh", ROOT / "include" / "mcb200.h"]
+HEADERS = [PKG / "csrc" / "mcb_device.cuh", PKG / "csrc" / "mcb_kernels.cuh", PKG / "csrc" / "mcb_verlet.cuh", PKG / "csrc" / "mcb_verlet2.cuh", PKG / "csrc" / "mcb_cells.cuh", ROOT / "include" / "mcb200.h"]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-shared", "-Xcompiler", "-fPIC"]

@@ -7,6 +7,7 @@
 #include "../../include/mcb200.h"
 #include "mcb_kernels.cuh"
 #include "mcb_verlet.cuh"
+#include "mcb_verlet2.cuh"
 #include "mcb_cells.cuh"
 
 #include <cmath>
@@ -694,7 +695,14 @@ extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, i
     if (uniforms) { if (h->coul) launch_run_ubuf<true>(h, nsteps, cap, d_consumed, d_steps); else launch_run_ubuf<false>(h, nsteps, cap, d_consumed, d_steps); }
     else {
         CK(h, cudaMemsetAsync(d_consumed, 0, sizeof(long long) * nc, h->stream));
-        if (h->vl.idx) {
+        const size_t vl2_bytes = (size_t)vl2_smem_doubles(h->g) * 8;
+        if (h->vl.idx && vl2_bytes <= 227 * 1024 && !getenv("MCB200_NO_VL2")) {
+            // two warps per chain, two steps in flight (mcb_verlet2.cuh)
+            set_smem_attr(h, k_run_vl2<true>, vl2_bytes); set_smem_attr(h, k_run_vl2<false>, vl2_bytes);
+            if (h->coul) k_run_vl2<true><<<h->n_chains, 64, vl2_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);
+            else k_run_vl2<false><<<h->n_chains, 64, vl2_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);
+            h->vl.trust = 1;
+        } else if (h->vl.idx) {
             set_smem_attr(h, k_run_vl<true>, h->smem_spec_bytes); set_smem_attr(h, k_run_vl<false>, h->smem_spec_bytes);
             if (h->coul) k_run_vl<true><<<h->n_chains, 32, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);
             else k_run_vl<false><<<h->n_chains, 32, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);

@@ -1,0 +1,378 @@
+// mcb_verlet2.cuh — k_run_vl2: k_run_vl with TWO warps per chain and two consecutive steps in flight.
+//
+// A box whose matrix lives in global memory needs ~55 KB of shared memory per chain, so an SM holds four chains
+// and, with one warp per chain, one warp per scheduler: every global-memory and shuffle latency of a step is
+// exposed.  Here warp 0 evaluates step k and warp 1 step k+1 of the same chain against the same committed state.
+// Warp 1 also decides whether its step would have seen anything that step k's move changes: the same molecule;
+// molecule i_k inside the cutoff of its trial position before or after i_k's own move; molecule i_k inside the
+// cutoff of i_{k+1}'s committed position before or after (that entry of the old row feeds dE).  It can do so alone
+// because step k's trial position only needs the pre-drawn ring and the committed coordinates.  After one
+// exchange through shared memory both warps know both decisions: step k is committed by warp 0 if accepted; step
+// k+1 stands unless step k was accepted and the test above fired, and is then committed by warp 1.  A discarded
+// step is evaluated again in the next batch with the same uniforms, so the chain is the sequential one, decision
+// for decision.  In a box of 240 molecules one step in eleven is discarded.
+//
+// Warp 1 works in a small area (64 + nsolp partner slots: what a neighbour list can yield); when its step cannot
+// use its list (trial position beyond skin/2, overflowed list, lists off) the batch is one step long.
+#pragma once
+
+#include "mcb_verlet.cuh"
+
+namespace mcb {
+
+struct Vl2X { double dE; int flags, nn; };   // flags: 1 accept, 2 used8, 4 clamped, 8 far, 16 evaluated, 32 depends on the step before
+
+__host__ __device__ inline int vl2_small_slots(const Geo &g) { return VL_K + g.nsolp; }
+__host__ __device__ inline int vl2_list_doubles(int slots) { return (((slots + 1) / 2) + 1) & ~1; }   // ints, padded to 16 bytes
+__host__ __device__ inline int vl2_smem_doubles(const Geo &g)
+{
+    const int big = g.Np + g.nsolp, small = vl2_small_slots(g);
+    return g.stage_doubles + vl2_list_doubles(big) + 4 * big + vl2_list_doubles(small) + 4 * small + 64 + 6 * 64 + 32 + g.Np + 8;
+}
+
+template <bool COUL>
+__global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl,
+                                                long long nsteps, long long *out_steps, VerletBufs vb)
+{
+    extern __shared__ __align__(16) double smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int c = blockIdx.x;
+    const int N = g.N, Np = g.Np, MS = g.MS, nsolp = g.nsolp;
+    const unsigned lt = (1u << lane) - 1u;
+    double *gimg = images + (size_t)c * g.image_doubles;
+    double *img = smem;
+    {
+        const double2 *src = reinterpret_cast<const double2 *>(gimg);
+        double2 *dst = reinterpret_cast<double2 *>(img);
+        for (int k = tid; k < g.stage_doubles / 2; k += 64) dst[k] = src[k];
+    }
+    double *const mat = matg + (size_t)c * N * MS;
+    double *const com = img + g.o_com, *const hoek = img + g.o_hoek, *const energy = img + g.o_energy;
+    double *const sites = img + g.o_sites;
+    const double *const tabAB = img + g.o_tabAB, *const tabQ = img + g.o_tabQ;
+    const int a = lane & 3, sub = lane >> 2;
+    // shared-memory plan behind the image: big work area (warp 0), small one (warp 1), ring, row sums, exchange
+    const int big = Np + nsolp, small = vl2_small_slots(g);
+    double *p = smem + g.stage_doubles;
+    int *const list_a = reinterpret_cast<int *>(p); p += vl2_list_doubles(big);
+    double *const epart_a = p; p += 4 * big;
+    int *const list_b = reinterpret_cast<int *>(p); p += vl2_list_doubles(small);
+    double *const epart_b = p; p += 4 * small;
+    double *const ring_thr = p; p += 64;
+    double *const ring_rv = p; p += 6 * 64;
+    int *const ring_i = reinterpret_cast<int *>(p); p += 32;
+    double *const rowsum = p; p += Np;
+    Vl2X *const xch = reinterpret_cast<Vl2X *>(p);
+    int *const list = warp == 0 ? list_a : list_b;
+    double *const epart = warp == 0 ? epart_a : epart_b;
+    unsigned short *const vidx = vb.idx + (size_t)c * N * VL_K;
+    int *const vcnt = vb.cnt + (size_t)c * (N + 2);
+    double *const vref = vb.ref + (size_t)c * 3 * Np;
+    const double rl = g.cutoff + vb.skin, rl2 = rl * rl, h2 = 0.25 * vb.skin * vb.skin;
+    ChainCtl s = ctl[c];
+    for (int q = lane; q < (warp == 0 ? big : small); q += 32) list[q] = q < nsolp ? N + q : 0;   // solute slots first; the rest valid indices
+    __syncthreads();
+    for (int j = tid; j < N; j += 64) {   // row sums from the stored matrix (symmetric: column sums, coalesced)
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+        int i = 0;
+        for (; i + 3 < N; i += 4) {
+            a0 += mat[(size_t)i * MS + j]; a1 += mat[(size_t)(i + 1) * MS + j];
+            a2 += mat[(size_t)(i + 2) * MS + j]; a3 += mat[(size_t)(i + 3) * MS + j];
+        }
+        for (; i < N; ++i) a0 += mat[(size_t)i * MS + j];
+        rowsum[j] = (a0 + a1) + (a2 + a3);
+    }
+    __syncthreads();
+    {
+        double acc = 0.0;
+        for (int i = lane; i < N; i += 32) acc += fma(0.5, rowsum[i], energy[i]);
+        s.toteng = warp_sum(acc);
+    }
+    // lists are usable only if the reference's minimum image is a true metric: all centres of mass inside the box
+    bool inside = true;
+    for (int j = lane; j < N; j += 32) inside = inside && fabs(com[j]) <= g.boxl && fabs(com[Np + j]) <= g.boxl && fabs(com[2 * Np + j]) <= g.boxl;
+    const bool lists_on = __all_sync(FULL, inside);
+    bool need_rebuild = lists_on && !(vb.trust && vcnt[N + 1] == 1);
+
+    const double relx = rel.r[3 * a], rely = rel.r[3 * a + 1], relz = rel.r[3 * a + 2];
+    const int wpair = rel.n_sites * rel.n_sites, wsol = rel.n_sites * g.nsol;
+    const double neg_inv_rt = -1000.0 / (8.314 * s.temperature);
+    const int rr = min(max(lane - 1, 0), 5);
+    const bool isang = rr >= 3;
+    const int kk = isang ? rr - 3 : rr;
+    double *const base = (isang ? hoek : com) + kk * Np;
+    const double period = isang ? TAU_D : g.boxl2, half = isang ? PI_D : g.boxl;
+    const double inv_half = isang ? 1.0 / PI_D : g.inv_boxl;
+    int adj_count = (int)(s.step % s.nadj);
+    int done = 0;
+    unsigned nsuc = 0, nacc = (unsigned)s.naccept, racc = 0, nclamp = 0, n_used8 = 0, prod_acc = 0, nrebuild = 0;
+    unsigned long long sum_nn = 0;
+    const unsigned long long step0 = (unsigned long long)s.step;
+    const int nsteps_i = (int)min(nsteps, (long long)0x3fffffff);
+    int ring_hi = 0;                                               // the ring holds the launch-local steps [ring_hi - 64, ring_hi)
+    const int ring0 = (int)(step0 & 63ULL);
+    const long long pf = s.start_prod - (long long)step0 - 1;     // launch-local index of the first production step (:760)
+    const int prod_from = pf <= 0 ? 0 : (pf > 0x3fffffff ? 0x7fffffff : (int)pf);
+    // list of a later step's molecule, fetched ahead: count, candidates, build position; p_step says for which step
+    int p_cnt = -1, p_idx[2] = {0, 0}, p_step = -1;
+    double p_rfx = 0.0, p_rfy = 0.0, p_rfz = 0.0;
+
+    while (done < nsteps_i) {
+        if (need_rebuild) {
+            // ---- (re)build every list from the current centres of mass, which become the reference positions
+            for (int j = tid; j < 3 * Np; j += 64) vref[j] = com[j];
+            for (int m = warp; m < N; m += 2) {
+                const double mx = com[m], my = com[Np + m], mz = com[2 * Np + m];
+                int cnt = 0;
+                for (int c0 = 0; c0 < N; c0 += 32) {
+                    const int j = c0 + lane;
+                    const bool in = j < N && j != m && !(pair_r2(com[j] - mx, com[Np + j] - my, com[2 * Np + j] - mz, g) > rl2);
+                    const unsigned b = __ballot_sync(FULL, in);
+                    const int pos = cnt + __popc(b & lt);
+                    if (in && pos < VL_K) vidx[(size_t)m * VL_K + pos] = (unsigned short)j;
+                    cnt += __popc(b);
+                }
+                if (lane == 0) vcnt[m] = cnt > VL_K ? -1 : cnt;
+            }
+            need_rebuild = false;
+            p_step = -1;
+            nrebuild++;
+            __syncthreads();
+        }
+        if (done + 4 > ring_hi) {                                   // pre-draw 32 steps, one per lane (as k_run_spec); warp 0 fills
+            if (warp == 0) {
+                const unsigned long long sidx = step0 + (unsigned)(ring_hi + lane);
+                const int e = (int)(sidx & 63ULL);
+                const double u0 = stream_uniform(s.rng_key, 8ULL * sidx);
+                int ii = (int)(u0 * (double)N) + 1;                 // MCINIT, MonteCarlo.F90:697-698
+                if (g.quirk31 && ii == 31) ii = 30;
+                ring_i[e] = min(ii, N) - 1;
+#pragma unroll
+                for (int q = 0; q < 6; ++q) {
+                    const double rvu = (stream_uniform(s.rng_key, 8ULL * sidx + 1 + q) - 0.5) * 2.0;
+                    ring_rv[6 * e + q] = (q < 3 ? INV_SQRT3 : 1.0) * rvu;
+                }
+                ring_thr[e] = log(stream_uniform(s.rng_key, 8ULL * sidx + 7)) * (1.0 / LN_E_F32);
+            }
+            ring_hi += 32;
+            __syncthreads();
+        }
+        // a batch never runs past the launch or past a step-size adaptation
+        const int limit = min(2, min(nsteps_i - done, s.nadj - adj_count));
+        const bool active = warp < limit;
+        const int k = done + warp;
+        const int ring_e = (ring0 + k) & 63;
+        const int i = ring_i[ring_e];
+        const double thr = ring_thr[ring_e];
+        const double old_tot = rowsum[i] + energy[i];
+        const double old_part = lane == 0 ? old_tot : 0.0;
+        // ---- candidates of molecule i (fetched during an earlier batch if the guess of this step's index was right)
+        if (lists_on && p_step != k) {
+            p_cnt = vcnt[i];
+            p_idx[0] = (int)vidx[(size_t)i * VL_K + lane]; p_idx[1] = (int)vidx[(size_t)i * VL_K + 32 + lane];
+            p_rfx = vref[i]; p_rfy = vref[Np + i]; p_rfz = vref[2 * Np + i];
+        }
+        const int cnt = lists_on ? p_cnt : -1;
+        int cj[2];
+        double cold[2];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) cj[q] = lane + 32 * q < cnt ? p_idx[q] : -1;
+        const double rfx = p_rfx, rfy = p_rfy, rfz = p_rfz;
+#pragma unroll
+        for (int q = 0; q < 2; ++q) cold[q] = cj[q] >= 0 ? mat[(size_t)i * MS + cj[q]] : 0.0;
+        if (lists_on) {   // this warp's step of the next batch if both steps of this one are committed
+            const int in = ring_i[(ring0 + k + 2) & 63];
+            p_cnt = vcnt[in];
+            p_idx[0] = (int)vidx[(size_t)in * VL_K + lane]; p_idx[1] = (int)vidx[(size_t)in * VL_K + 32 + lane];
+            p_rfx = vref[in]; p_rfy = vref[Np + in]; p_rfz = vref[2 * Np + in];
+            p_step = k + 2;
+        }
+        // ---- trial move (MCINIT :699-712), RotMatrix of the own site
+        const double rv = (isang ? s.dhoekmax : s.dposmax) * ring_rv[6 * ring_e + rr];
+        const double nv = wrap_fma(base[i] + rv, period, half, inv_half);
+        double sn, cs;
+        sincos_small(nv, sn, cs);
+        const double ncx = shfl_d(nv, 1), ncy = shfl_d(nv, 2), ncz = shfl_d(nv, 3);
+        const double c1 = shfl_d(cs, 4), s1 = shfl_d(sn, 4), c2 = shfl_d(cs, 5), s2 = shfl_d(sn, 5), c3 = shfl_d(cs, 6), s3 = shfl_d(sn, 6);
+        double sx, sy, sz;
+        rotate_site(c1, s1, c2, s2, c3, s3, relx, rely, relz, ncx, ncy, ncz, sx, sy, sz);
+        const bool far = !lists_on || pair_r2(ncx - rfx, ncy - rfy, ncz - rfz, g) > h2;
+        const bool use_list = cnt >= 0 && !far;
+        // warp 0 can always evaluate (its work area holds a full scan); warp 1 only from its list
+        const bool evaluate = active && (warp == 0 || use_list);
+        // ---- warp 1: would step k-1's move, if accepted, change anything this step looks at?
+        bool dep = false;
+        if (warp == 1) {
+            const int e0 = (ring0 + done) & 63, i0 = ring_i[e0];
+            const double m0 = wrap_fma(com[min(rr, 2) * Np + i0] + s.dposmax * ring_rv[6 * e0 + min(rr, 2)], g.boxl2, g.boxl, g.inv_boxl);
+            const double n0x = shfl_d(m0, 1), n0y = shfl_d(m0, 2), n0z = shfl_d(m0, 3);     // step k-1's trial centre of mass
+            const double ox = com[i0], oy = com[Np + i0], oz = com[2 * Np + i0];           // its committed one
+            const double bx = com[i], by = com[Np + i], bz = com[2 * Np + i];              // this step's molecule, committed
+            double tx = ox - ncx, ty = oy - ncy, tz = oz - ncz;                            // lane 0: was a partner of the trial position
+            if (lane == 1) { tx = n0x - ncx; ty = n0y - ncy; tz = n0z - ncz; }             // lane 1: would become one
+            if (lane == 2) { tx = ox - bx; ty = oy - by; tz = oz - bz; }                   // lane 2: entry of the old row, as committed
+            if (lane == 3) { tx = n0x - bx; ty = n0y - by; tz = n0z - bz; }                // lane 3: that entry after the move
+            const bool hit = lane < 4 && !(pair_r2(tx, ty, tz, g) > g.cut2);
+            dep = __ballot_sync(FULL, hit) != 0u || i0 == i;
+        }
+        // ---- centre-of-mass gate (:804-813) on the candidates, or on everybody (warp 0 only)
+        int nn = 0;
+        bool cin[2] = {false, false};
+        int cslot[2] = {0, 0};
+        double dE = 0.0, esol = 0.0;
+        double cval[2] = {0.0, 0.0}, cdel[2] = {0.0, 0.0};
+        bool cchg[2] = {false, false};
+        bool clamped = false, used8 = false, accept = false;
+        if (evaluate) {
+            if (use_list) {
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {   // every lane computes a distance (empty lanes on molecule 0), the guard selects
+                    const int jj = cj[q] >= 0 ? cj[q] : 0;
+                    const double r2 = pair_r2(com[jj] - ncx, com[Np + jj] - ncy, com[2 * Np + jj] - ncz, g);
+                    cin[q] = !((cj[q] >= 0 ? r2 : DBL_HUGE) > g.cut2);
+                }
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    const unsigned b = __ballot_sync(FULL, cin[q]);
+                    cslot[q] = nsolp + nn + __popc(b & lt);
+                    if (cin[q]) list[cslot[q]] = cj[q];
+                    nn += __popc(b);
+                }
+            } else {
+                for (int c0 = 0; c0 < N; c0 += 32) {
+                    const int j = c0 + lane;
+                    const bool in = j < N && j != i && !(pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2);
+                    const unsigned b = __ballot_sync(FULL, in);
+                    if (in) list[nsolp + nn + __popc(b & lt)] = j;
+                    nn += __popc(b);
+                }
+            }
+            __syncwarp();
+            // ---- site pairs (calcLJ / CalcLJ_SV), staged
+            const int nslots = nsolp + nn;
+            double lane_tot = 0.0;
+            for (int sb = 0; sb < nslots; sb += 2 * 8)   // the same number of passes on every lane
+                lane_tot += items_staged<COUL, 2>(g, sites, tabAB, tabQ, list, nsolp, nslots, sb + sub, 8, a, sx, sy, sz, epart);
+            dE = lane_tot - old_part;
+            __syncwarp();
+            // what an accepted move would write for this lane's candidates: formed here, in the shadow of the reduction
+            if (use_list) {
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    const int sl = cin[q] ? cslot[q] : 0;
+                    const double2 e01 = *reinterpret_cast<const double2 *>(epart + 4 * sl), e23 = *reinterpret_cast<const double2 *>(epart + 4 * sl + 2);
+                    cval[q] = cin[q] ? (e01.x + e01.y) + (e23.x + e23.y) : 0.0;
+                    cdel[q] = cval[q] - cold[q];
+                    cchg[q] = cj[q] >= 0 && (cin[q] || cold[q] != 0.0);
+                }
+            }
+            if (sub < nsolp) esol = epart[4 * sub + a];
+            if (nsolp > 8) {
+#pragma unroll 1
+                for (int p2 = sub + 8; p2 < nsolp; p2 += 8) esol += epart[4 * p2 + a];
+            }
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
+            // ---- METROPOLIS (:720-788) on DELTA = dE
+            const double exponent = dE * neg_inv_rt;
+            clamped = !(fabs(dE) <= DBL_HUGE);
+            used8 = !clamped && exponent >= -75.0 && exponent < 0.0;
+            accept = !clamped && (exponent >= 0.0 || (used8 && thr <= exponent));
+        }
+        if (lane == 0) {
+            Vl2X x;
+            x.dE = dE; x.nn = nn;
+            x.flags = (accept ? 1 : 0) | (used8 ? 2 : 0) | (clamped ? 4 : 0) | (far ? 8 : 0) | (evaluate ? 16 : 0) | (dep ? 32 : 0);
+            xch[warp] = x;
+        }
+        __syncthreads();
+        const Vl2X x0 = xch[0], x1 = xch[1];
+        // step k+1 stands unless it was not evaluated, or step k was accepted and touched what it had looked at
+        const int progress = (x1.flags & 16) && !((x0.flags & 1) && (x1.flags & 32)) ? 2 : 1;
+        const int nslots = nsolp + nn;
+        // ---- commits, one after the other: two standing steps can share a neighbour whose row sum both adjust
+#pragma unroll
+        for (int cw = 0; cw < 2; ++cw) {
+            if (cw == 1) { if (progress == 2 && (x1.flags & 1)) __syncthreads(); else break; }   // uniform over the block
+            if (warp == cw && accept) {
+                if (use_list) {
+#pragma unroll
+                    for (int q = 0; q < 2; ++q)
+                        if (cchg[q]) {   // SS(i,j) = SS(j,i) = EN inside the cutoff (:819-820), 0 for a partner that left it
+                            const int j = cj[q];
+                            rowsum[j] += cdel[q];
+                            mat[(size_t)i * MS + j] = cval[q]; mat[(size_t)j * MS + i] = cval[q];
+                        }
+                } else {
+                    // full scan: partners that left the cutoff, then the partners inside it
+                    for (int j = lane; j < N; j += 32) {
+                        const double old = mat[(size_t)i * MS + j];
+                        if (old != 0.0 && j != i && pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2) {
+                            rowsum[j] -= old;
+                            mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0;
+                        }
+                    }
+                    for (int sl = nsolp + lane; sl < nslots; sl += 32) {
+                        const int j = list[sl];
+                        const double e = (epart[4 * sl] + epart[4 * sl + 1]) + (epart[4 * sl + 2] + epart[4 * sl + 3]);
+                        rowsum[j] += e - mat[(size_t)i * MS + j];
+                        mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
+                    }
+                }
+                if (lane >= 1 && lane <= 6) base[i] = nv;
+                if (lane < 4) {
+                    sites[SITE_DOUBLES * i + 3 * a] = sx; sites[SITE_DOUBLES * i + 3 * a + 1] = sy; sites[SITE_DOUBLES * i + 3 * a + 2] = sz;
+                }
+                if (lane == 0) { energy[i] = esol; rowsum[i] = (dE + old_tot) - esol; }
+            }
+        }
+        // ---- bookkeeping in step order (both warps keep the same copy)
+#pragma unroll
+        for (int gg = 0; gg < 2; ++gg) {
+            if (gg < progress) {
+                const Vl2X x = gg == 0 ? x0 : x1;
+                const bool acc = (x.flags & 1) != 0;
+                n_used8 += (x.flags >> 1) & 1;
+                nclamp += (x.flags >> 2) & 1;
+                sum_nn += (unsigned)x.nn;
+                s.last_delta = x.dE;
+                const bool in_prod = done + gg >= prod_from;        // selects instead of branches: adding 0.0 changes nothing
+                nsuc += acc; nacc += acc;
+                s.toteng += acc ? x.dE : 0.0;
+                s.production += acc && in_prod ? s.toteng : 0.0; prod_acc += acc && in_prod;
+                const double te = in_prod ? s.toteng : 0.0;
+                s.sum_e += te; s.sum_e2 = fma(te, te, s.sum_e2);
+                if (lists_on && acc && (x.flags & 8)) need_rebuild = true;   // the molecule now sits more than skin/2 from its build position
+            }
+        }
+        racc = nacc;
+        adj_count += progress;
+        if (adj_count == s.nadj) {                                  // mod(I, NADJ) == 0, :766-777
+            adj_count = 0;
+            const double ratio = (double)((float)nacc / (float)s.nadj);
+            if (ratio > 0.5) { s.dposmax *= (1.0 + s.padj); s.dhoekmax *= (1.0 + s.padj); }
+            else if (ratio < 0.5) { s.dposmax *= (1.0 - s.padj); s.dhoekmax *= (1.0 - s.padj); }
+            s.dposmax = fmax(s.dposmax, s.dposmin); s.dhoekmax = fmax(s.dhoekmax, s.dhoekmin);
+            nacc = 0;
+        }
+        done += progress;
+        __syncthreads();
+    }
+    {
+        const int n_mut = g.o_sites + SITE_DOUBLES * N;
+        for (int qq = tid; qq < n_mut; qq += 64) gimg[qq] = img[qq];
+    }
+    if (tid == 0) {
+        s.step += done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.prod_acc += prod_acc;
+        s.uused += 7LL * done + n_used8;
+        s.nstat += done > prod_from ? done - prod_from : 0;
+        s.sitepairs += (long long)wpair * (long long)sum_nn + (long long)wsol * done;
+        if (done > 0) s.ratio = (double)((float)racc / (float)s.nadj);
+        ctl[c] = s;
+        if (out_steps) out_steps[c] = done;
+        vcnt[N] = (int)nrebuild;
+        vcnt[N + 1] = lists_on && !need_rebuild ? 1 : 0;
+    }
+}
+
+}  // namespace mcb
