@@ -31,6 +31,7 @@ struct mcb_handle {
     CellGrid cells{};       // cell list of the matrix-free energy (mcb_cells.cuh); nc == 0: not in use
     int ncell = 0;
     VerletBufs vl{};        // neighbour lists of k_run_vl (large boxes); idx == nullptr: not in use
+    int vl2_w = 0;          // warps per chain of k_run_vl2: 0 not chosen yet, -1 does not fit
     cudaStream_t stream = nullptr;
     double *images = nullptr, *matg = nullptr, *work = nullptr;
     ChainCtl *ctl = nullptr;
@@ -671,6 +672,41 @@ static void launch_run_spec_any(mcb_t *h, long long nsteps, long long *d_steps)
     }
 }
 
+template <int W>
+static void launch_vl2(mcb_t *h, long long nsteps, long long *d_steps)
+{
+    const size_t bytes = (size_t)vl2_smem_doubles(h->g, W) * 8;
+    if (h->coul) k_run_vl2<true, W><<<h->n_chains, 32 * W, bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->work, h->ctl, nsteps, d_steps, h->vl);
+    else k_run_vl2<false, W><<<h->n_chains, 32 * W, bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->work, h->ctl, nsteps, d_steps, h->vl);
+}
+
+template <int W>
+static int vl2_blocks_per_sm(mcb_t *h)
+{
+    const size_t bytes = (size_t)vl2_smem_doubles(h->g, W) * 8;
+    if (bytes > 227 * 1024) return 0;
+    if (set_smem_attr(h, k_run_vl2<true, W>, bytes) || set_smem_attr(h, k_run_vl2<false, W>, bytes)) return 0;
+    int nb = 0;
+    cudaError_t e = h->coul ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_run_vl2<true, W>, 32 * W, bytes)
+                            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_run_vl2<false, W>, 32 * W, bytes);
+    return e == cudaSuccess ? nb : 0;
+}
+
+// Warps per chain for k_run_vl2: the widest variant that still keeps every chain resident at once; if none does, the
+// one that puts most warps on an SM.  -1: the kernel does not fit (k_run_vl is used).  MCB200_VL2_W overrides (tuning).
+static int pick_vl2_width(mcb_t *h)
+{
+    int dev = 0, nsm = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
+    const int occ[5] = {0, 0, vl2_blocks_per_sm<2>(h), vl2_blocks_per_sm<3>(h), vl2_blocks_per_sm<4>(h)};
+    if (const char *t = getenv("MCB200_VL2_W")) { const int w = atoi(t); if (w >= 2 && w <= 4 && occ[w] > 0) return w; }
+    for (int w = 4; w >= 2; --w) if (occ[w] > 0 && (long long)occ[w] * nsm >= h->n_chains) return w;
+    int best = -1, best_warps = 0;
+    for (int w = 2; w <= 4; ++w) if (occ[w] * w > best_warps) { best_warps = occ[w] * w; best = w; }
+    return best;
+}
+
 extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, int64_t cap, int64_t *consumed, int64_t *steps_done)
 {
     if (!h) return 1;
@@ -695,12 +731,14 @@ extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, i
     if (uniforms) { if (h->coul) launch_run_ubuf<true>(h, nsteps, cap, d_consumed, d_steps); else launch_run_ubuf<false>(h, nsteps, cap, d_consumed, d_steps); }
     else {
         CK(h, cudaMemsetAsync(d_consumed, 0, sizeof(long long) * nc, h->stream));
-        const size_t vl2_bytes = (size_t)vl2_smem_doubles(h->g) * 8;
-        if (h->vl.idx && vl2_bytes <= 227 * 1024 && !getenv("MCB200_NO_VL2")) {
-            // two warps per chain, two steps in flight (mcb_verlet2.cuh)
-            set_smem_attr(h, k_run_vl2<true>, vl2_bytes); set_smem_attr(h, k_run_vl2<false>, vl2_bytes);
-            if (h->coul) k_run_vl2<true><<<h->n_chains, 64, vl2_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);
-            else k_run_vl2<false><<<h->n_chains, 64, vl2_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);
+        if (h->vl.idx && !h->vl2_w && !getenv("MCB200_NO_VL2")) h->vl2_w = pick_vl2_width(h);
+        if (h->vl.idx && h->vl2_w > 0) {
+            // W warps per chain, W consecutive steps in flight (mcb_verlet2.cuh)
+            switch (h->vl2_w) {
+                case 4: launch_vl2<4>(h, nsteps, d_steps); break;
+                case 3: launch_vl2<3>(h, nsteps, d_steps); break;
+                default: launch_vl2<2>(h, nsteps, d_steps); break;
+            }
             h->vl.trust = 1;
         } else if (h->vl.idx) {
             set_smem_attr(h, k_run_vl<true>, h->smem_spec_bytes); set_smem_attr(h, k_run_vl<false>, h->smem_spec_bytes);

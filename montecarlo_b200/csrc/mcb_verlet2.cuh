@@ -1,39 +1,44 @@
-// mcb_verlet2.cuh — k_run_vl2: k_run_vl with TWO warps per chain and two consecutive steps in flight.
+// mcb_verlet2.cuh — k_run_vl2<W>: k_run_vl with W warps per chain and W consecutive steps in flight.
 //
-// A box whose matrix lives in global memory needs ~55 KB of shared memory per chain, so an SM holds four chains
+// A box whose matrix lives in global memory needs ~45-55 KB of shared memory per chain, so an SM holds four chains
 // and, with one warp per chain, one warp per scheduler: every global-memory and shuffle latency of a step is
-// exposed.  Here warp 0 evaluates step k and warp 1 step k+1 of the same chain against the same committed state.
-// Warp 1 also decides whether its step would have seen anything that step k's move changes: the same molecule;
-// molecule i_k inside the cutoff of its trial position before or after i_k's own move; molecule i_k inside the
-// cutoff of i_{k+1}'s committed position before or after (that entry of the old row feeds dE).  It can do so alone
-// because step k's trial position only needs the pre-drawn ring and the committed coordinates.  After one
-// exchange through shared memory both warps know both decisions: step k is committed by warp 0 if accepted; step
-// k+1 stands unless step k was accepted and the test above fired, and is then committed by warp 1.  A discarded
-// step is evaluated again in the next batch with the same uniforms, so the chain is the sequential one, decision
-// for decision.  In a box of 240 molecules one step in eleven is discarded.
+// exposed.  Here warp w evaluates step k+w of the same chain against the same committed state.  Each warp w > 0
+// also decides, for every earlier step j of the batch, whether its own step would have seen anything that step
+// j's move changes: the same molecule; molecule i_j inside the cutoff of its trial position before or after i_j's
+// own move; molecule i_j inside the cutoff of its molecule's committed position before or after (that entry of
+// the old row feeds dE).  It can do so alone, because step j's trial position only needs the pre-drawn ring and the
+// committed coordinates.  After one exchange through shared memory every warp knows every decision: step k+w
+// stands if all steps before it stand and no ACCEPTED one of them fired the test above; standing accepted steps
+// are committed one after the other, each by its own warp.  The first step that does not stand, and everything
+// after it, is evaluated again in the next batch with the same uniforms, so the chain is the sequential one,
+// decision for decision.  In a box of 240 molecules about one step in eleven fails against its predecessor.
 //
-// Warp 1 works in a small area (64 + nsolp partner slots: what a neighbour list can yield); when its step cannot
-// use its list (trial position beyond skin/2, overflowed list, lists off) the batch is one step long.
+// Every warp works in a small area (VL_K + nsolp partner slots: what a neighbour list can yield); a step that
+// cannot use its list (trial position beyond skin/2, overflowed list, lists off) is evaluated by warp 0 only, with
+// the full scan, in the chain's global work area - the batch is then that one step.
 #pragma once
 
 #include "mcb_verlet.cuh"
 
 namespace mcb {
 
-struct Vl2X { double dE; int flags, nn; };   // flags: 1 accept, 2 used8, 4 clamped, 8 far, 16 evaluated, 32 depends on the step before
+struct Vl2X { double dE; int flags, nn; };   // flags: 1 accept, 2 used8, 4 clamped, 8 far, 16 evaluated; bits 8..15: depends on earlier step j of the batch
+constexpr int VL2_MAX_W = 8;
 
 __host__ __device__ inline int vl2_small_slots(const Geo &g) { return VL_K + g.nsolp; }
 __host__ __device__ inline int vl2_list_doubles(int slots) { return (((slots + 1) / 2) + 1) & ~1; }   // ints, padded to 16 bytes
-__host__ __device__ inline int vl2_smem_doubles(const Geo &g)
+__host__ __device__ inline int vl2_smem_doubles(const Geo &g, int w)
 {
-    const int big = g.Np + g.nsolp, small = vl2_small_slots(g);
-    return g.stage_doubles + vl2_list_doubles(big) + 4 * big + vl2_list_doubles(small) + 4 * small + 64 + 6 * 64 + 32 + g.Np + 8;
+    const int small = vl2_small_slots(g);
+    return g.stage_doubles + w * (vl2_list_doubles(small) + 4 * small) + 64 + 6 * 64 + 32 + g.Np + 2 * VL2_MAX_W;
 }
 
-template <bool COUL>
-__global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl,
-                                                long long nsteps, long long *out_steps, VerletBufs vb)
+template <bool COUL, int W>
+__global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteRel rel, double *images, double *matg, double *workg,
+                                                                    ChainCtl *ctl, long long nsteps, long long *out_steps, VerletBufs vb)
 {
+    static_assert(W >= 2 && W <= VL2_MAX_W, "2..8 warps per chain");
+    constexpr int NT = 32 * W;
     extern __shared__ __align__(16) double smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int c = blockIdx.x;
@@ -44,35 +49,36 @@ __global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *imag
     {
         const double2 *src = reinterpret_cast<const double2 *>(gimg);
         double2 *dst = reinterpret_cast<double2 *>(img);
-        for (int k = tid; k < g.stage_doubles / 2; k += 64) dst[k] = src[k];
+        for (int k = tid; k < g.stage_doubles / 2; k += NT) dst[k] = src[k];
     }
     double *const mat = matg + (size_t)c * N * MS;
     double *const com = img + g.o_com, *const hoek = img + g.o_hoek, *const energy = img + g.o_energy;
     double *const sites = img + g.o_sites;
     const double *const tabAB = img + g.o_tabAB, *const tabQ = img + g.o_tabQ;
     const int a = lane & 3, sub = lane >> 2;
-    // shared-memory plan behind the image: big work area (warp 0), small one (warp 1), ring, row sums, exchange
-    const int big = Np + nsolp, small = vl2_small_slots(g);
-    double *p = smem + g.stage_doubles;
-    int *const list_a = reinterpret_cast<int *>(p); p += vl2_list_doubles(big);
-    double *const epart_a = p; p += 4 * big;
-    int *const list_b = reinterpret_cast<int *>(p); p += vl2_list_doubles(small);
-    double *const epart_b = p; p += 4 * small;
+    // shared-memory plan behind the image: one small work area per warp (VL_K + nsolp partner slots: what a list can
+    // yield), ring, row sums, exchange.  A step that needs the full scan runs on warp 0 in the chain's global work area.
+    const int small = vl2_small_slots(g);
+    double *p = smem + g.stage_doubles + warp * (vl2_list_doubles(small) + 4 * small);
+    int *const list = reinterpret_cast<int *>(p);
+    double *const epart = p + vl2_list_doubles(small);
+    int *const list_g = reinterpret_cast<int *>(workg + (size_t)c * g.work_doubles + g.o_list);
+    double *const epart_g = workg + (size_t)c * g.work_doubles + g.o_epart;
+    p = smem + g.stage_doubles + W * (vl2_list_doubles(small) + 4 * small);
     double *const ring_thr = p; p += 64;
     double *const ring_rv = p; p += 6 * 64;
     int *const ring_i = reinterpret_cast<int *>(p); p += 32;
     double *const rowsum = p; p += Np;
     Vl2X *const xch = reinterpret_cast<Vl2X *>(p);
-    int *const list = warp == 0 ? list_a : list_b;
-    double *const epart = warp == 0 ? epart_a : epart_b;
     unsigned short *const vidx = vb.idx + (size_t)c * N * VL_K;
     int *const vcnt = vb.cnt + (size_t)c * (N + 2);
     double *const vref = vb.ref + (size_t)c * 3 * Np;
     const double rl = g.cutoff + vb.skin, rl2 = rl * rl, h2 = 0.25 * vb.skin * vb.skin;
     ChainCtl s = ctl[c];
-    for (int q = lane; q < (warp == 0 ? big : small); q += 32) list[q] = q < nsolp ? N + q : 0;   // solute slots first; the rest valid indices
+    for (int q = lane; q < small; q += 32) list[q] = q < nsolp ? N + q : 0;   // solute slots first; the rest valid indices
+    if (warp == 0) for (int q = lane; q < nsolp; q += 32) list_g[q] = N + q;
     __syncthreads();
-    for (int j = tid; j < N; j += 64) {   // row sums from the stored matrix (symmetric: column sums, coalesced)
+    for (int j = tid; j < N; j += NT) {   // row sums from the stored matrix (symmetric: column sums, coalesced)
         double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
         int i = 0;
         for (; i + 3 < N; i += 4) {
@@ -120,8 +126,8 @@ __global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *imag
     while (done < nsteps_i) {
         if (need_rebuild) {
             // ---- (re)build every list from the current centres of mass, which become the reference positions
-            for (int j = tid; j < 3 * Np; j += 64) vref[j] = com[j];
-            for (int m = warp; m < N; m += 2) {
+            for (int j = tid; j < 3 * Np; j += NT) vref[j] = com[j];
+            for (int m = warp; m < N; m += W) {
                 const double mx = com[m], my = com[Np + m], mz = com[2 * Np + m];
                 int cnt = 0;
                 for (int c0 = 0; c0 < N; c0 += 32) {
@@ -139,7 +145,7 @@ __global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *imag
             nrebuild++;
             __syncthreads();
         }
-        if (done + 4 > ring_hi) {                                   // pre-draw 32 steps, one per lane (as k_run_spec); warp 0 fills
+        if (done + 2 * W > ring_hi) {                                   // pre-draw 32 steps, one per lane (as k_run_spec); warp 0 fills
             if (warp == 0) {
                 const unsigned long long sidx = step0 + (unsigned)(ring_hi + lane);
                 const int e = (int)(sidx & 63ULL);
@@ -158,7 +164,7 @@ __global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *imag
             __syncthreads();
         }
         // a batch never runs past the launch or past a step-size adaptation
-        const int limit = min(2, min(nsteps_i - done, s.nadj - adj_count));
+        const int limit = min(W, min(nsteps_i - done, s.nadj - adj_count));
         const bool active = warp < limit;
         const int k = done + warp;
         const int ring_e = (ring0 + k) & 63;
@@ -180,12 +186,12 @@ __global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *imag
         const double rfx = p_rfx, rfy = p_rfy, rfz = p_rfz;
 #pragma unroll
         for (int q = 0; q < 2; ++q) cold[q] = cj[q] >= 0 ? mat[(size_t)i * MS + cj[q]] : 0.0;
-        if (lists_on) {   // this warp's step of the next batch if both steps of this one are committed
-            const int in = ring_i[(ring0 + k + 2) & 63];
+        if (lists_on) {   // this warp's step of the next batch if all steps of this one are committed
+            const int in = ring_i[(ring0 + k + W) & 63];
             p_cnt = vcnt[in];
             p_idx[0] = (int)vidx[(size_t)in * VL_K + lane]; p_idx[1] = (int)vidx[(size_t)in * VL_K + 32 + lane];
             p_rfx = vref[in]; p_rfy = vref[Np + in]; p_rfz = vref[2 * Np + in];
-            p_step = k + 2;
+            p_step = k + W;
         }
         // ---- trial move (MCINIT :699-712), RotMatrix of the own site
         const double rv = (isang ? s.dhoekmax : s.dposmax) * ring_rv[6 * ring_e + rr];
@@ -200,20 +206,26 @@ __global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *imag
         const bool use_list = cnt >= 0 && !far;
         // warp 0 can always evaluate (its work area holds a full scan); warp 1 only from its list
         const bool evaluate = active && (warp == 0 || use_list);
-        // ---- warp 1: would step k-1's move, if accepted, change anything this step looks at?
-        bool dep = false;
-        if (warp == 1) {
-            const int e0 = (ring0 + done) & 63, i0 = ring_i[e0];
-            const double m0 = wrap_fma(com[min(rr, 2) * Np + i0] + s.dposmax * ring_rv[6 * e0 + min(rr, 2)], g.boxl2, g.boxl, g.inv_boxl);
-            const double n0x = shfl_d(m0, 1), n0y = shfl_d(m0, 2), n0z = shfl_d(m0, 3);     // step k-1's trial centre of mass
-            const double ox = com[i0], oy = com[Np + i0], oz = com[2 * Np + i0];           // its committed one
+        // ---- warps 1..: would the move of an earlier step j of this batch, if accepted, change anything this step looks
+        //      at?  Four lanes per earlier step, one distance test each; step j's trial centre of mass comes from the ring
+        //      and the committed coordinates (the same expression warp j evaluates).
+        int depmask = 0;
+        if (warp > 0) {
+            const int j = min(lane >> 2, warp - 1), t = lane & 3;
+            const int ej = (ring0 + done + j) & 63, ij = ring_i[ej];
+            const double ox = com[ij], oy = com[Np + ij], oz = com[2 * Np + ij];           // step j's molecule, committed
+            const double n0x = wrap_fma(ox + s.dposmax * ring_rv[6 * ej + 0], g.boxl2, g.boxl, g.inv_boxl);
+            const double n0y = wrap_fma(oy + s.dposmax * ring_rv[6 * ej + 1], g.boxl2, g.boxl, g.inv_boxl);
+            const double n0z = wrap_fma(oz + s.dposmax * ring_rv[6 * ej + 2], g.boxl2, g.boxl, g.inv_boxl);   // ... and at its trial position
             const double bx = com[i], by = com[Np + i], bz = com[2 * Np + i];              // this step's molecule, committed
-            double tx = ox - ncx, ty = oy - ncy, tz = oz - ncz;                            // lane 0: was a partner of the trial position
-            if (lane == 1) { tx = n0x - ncx; ty = n0y - ncy; tz = n0z - ncz; }             // lane 1: would become one
-            if (lane == 2) { tx = ox - bx; ty = oy - by; tz = oz - bz; }                   // lane 2: entry of the old row, as committed
-            if (lane == 3) { tx = n0x - bx; ty = n0y - by; tz = n0z - bz; }                // lane 3: that entry after the move
-            const bool hit = lane < 4 && !(pair_r2(tx, ty, tz, g) > g.cut2);
-            dep = __ballot_sync(FULL, hit) != 0u || i0 == i;
+            double tx = ox - ncx, ty = oy - ncy, tz = oz - ncz;                            // t = 0: was a partner of the trial position
+            if (t == 1) { tx = n0x - ncx; ty = n0y - ncy; tz = n0z - ncz; }                // t = 1: would become one
+            if (t == 2) { tx = ox - bx; ty = oy - by; tz = oz - bz; }                      // t = 2: entry of the old row, as committed
+            if (t == 3) { tx = n0x - bx; ty = n0y - by; tz = n0z - bz; }                   // t = 3: that entry after the move
+            const bool hit = (lane >> 2) < warp && (ij == i || !(pair_r2(tx, ty, tz, g) > g.cut2));
+            const unsigned hb = __ballot_sync(FULL, hit);
+#pragma unroll
+            for (int q = 0; q < W - 1; ++q) depmask |= ((hb >> (4 * q)) & 0xFu) ? (1 << q) : 0;
         }
         // ---- centre-of-mass gate (:804-813) on the candidates, or on everybody (warp 0 only)
         int nn = 0;
@@ -243,7 +255,7 @@ __global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *imag
                     const int j = c0 + lane;
                     const bool in = j < N && j != i && !(pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2);
                     const unsigned b = __ballot_sync(FULL, in);
-                    if (in) list[nsolp + nn + __popc(b & lt)] = j;
+                    if (in) list_g[nsolp + nn + __popc(b & lt)] = j;
                     nn += __popc(b);
                 }
             }
@@ -251,10 +263,16 @@ __global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *imag
             // ---- site pairs (calcLJ / CalcLJ_SV), staged
             const int nslots = nsolp + nn;
             double lane_tot = 0.0;
-            for (int sb = 0; sb < nslots; sb += 2 * 8)   // the same number of passes on every lane
-                lane_tot += items_staged<COUL, 2>(g, sites, tabAB, tabQ, list, nsolp, nslots, sb + sub, 8, a, sx, sy, sz, epart);
+            if (use_list) {
+                for (int sb = 0; sb < nslots; sb += 2 * 8)   // the same number of passes on every lane
+                    lane_tot += items_staged<COUL, 2>(g, sites, tabAB, tabQ, list, nsolp, nslots, sb + sub, 8, a, sx, sy, sz, epart);
+            } else {
+                for (int sb = 0; sb < nslots; sb += 2 * 8)
+                    lane_tot += items_staged<COUL, 2>(g, sites, tabAB, tabQ, list_g, nsolp, nslots, sb + sub, 8, a, sx, sy, sz, epart_g);
+            }
             dE = lane_tot - old_part;
             __syncwarp();
+            const double *const ep = use_list ? epart : epart_g;
             // what an accepted move would write for this lane's candidates: formed here, in the shadow of the reduction
             if (use_list) {
 #pragma unroll
@@ -266,10 +284,10 @@ __global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *imag
                     cchg[q] = cj[q] >= 0 && (cin[q] || cold[q] != 0.0);
                 }
             }
-            if (sub < nsolp) esol = epart[4 * sub + a];
+            if (sub < nsolp) esol = ep[4 * sub + a];
             if (nsolp > 8) {
 #pragma unroll 1
-                for (int p2 = sub + 8; p2 < nsolp; p2 += 8) esol += epart[4 * p2 + a];
+                for (int p2 = sub + 8; p2 < nsolp; p2 += 8) esol += ep[4 * p2 + a];
             }
 #pragma unroll
             for (int o = 16; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
@@ -282,19 +300,32 @@ __global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *imag
         if (lane == 0) {
             Vl2X x;
             x.dE = dE; x.nn = nn;
-            x.flags = (accept ? 1 : 0) | (used8 ? 2 : 0) | (clamped ? 4 : 0) | (far ? 8 : 0) | (evaluate ? 16 : 0) | (dep ? 32 : 0);
+            x.flags = (accept ? 1 : 0) | (used8 ? 2 : 0) | (clamped ? 4 : 0) | (far ? 8 : 0) | (evaluate ? 16 : 0) | (depmask << 8);
             xch[warp] = x;
         }
         __syncthreads();
-        const Vl2X x0 = xch[0], x1 = xch[1];
-        // step k+1 stands unless it was not evaluated, or step k was accepted and touched what it had looked at
-        const int progress = (x1.flags & 16) && !((x0.flags & 1) && (x1.flags & 32)) ? 2 : 1;
+        Vl2X xs[W];
+#pragma unroll
+        for (int q = 0; q < W; ++q) xs[q] = xch[q];
+        // step k+q stands if it was evaluated, every step before it stands, and no ACCEPTED earlier step touched what it looked at
+        int progress = 1;
+        unsigned acc_valid = xs[0].flags & 1u;
+#pragma unroll
+        for (int q = 1; q < W; ++q)
+            if (progress == q && (xs[q].flags & 16) && (((unsigned)xs[q].flags >> 8) & acc_valid) == 0u) {
+                progress = q + 1;
+                acc_valid |= (unsigned)(xs[q].flags & 1) << q;
+            }
         const int nslots = nsolp + nn;
         // ---- commits, one after the other: two standing steps can share a neighbour whose row sum both adjust
 #pragma unroll
-        for (int cw = 0; cw < 2; ++cw) {
-            if (cw == 1) { if (progress == 2 && (x1.flags & 1)) __syncthreads(); else break; }   // uniform over the block
-            if (warp == cw && accept) {
+        bool committed = false;
+#pragma unroll
+        for (int cw = 0; cw < W; ++cw) {
+            if (cw >= progress || !(xs[cw].flags & 1)) continue;                    // uniform over the block
+            if (committed) __syncthreads();
+            committed = true;
+            if (warp == cw) {
                 if (use_list) {
 #pragma unroll
                     for (int q = 0; q < 2; ++q)
@@ -313,8 +344,8 @@ __global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *imag
                         }
                     }
                     for (int sl = nsolp + lane; sl < nslots; sl += 32) {
-                        const int j = list[sl];
-                        const double e = (epart[4 * sl] + epart[4 * sl + 1]) + (epart[4 * sl + 2] + epart[4 * sl + 3]);
+                        const int j = list_g[sl];
+                        const double e = (epart_g[4 * sl] + epart_g[4 * sl + 1]) + (epart_g[4 * sl + 2] + epart_g[4 * sl + 3]);
                         rowsum[j] += e - mat[(size_t)i * MS + j];
                         mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
                     }
@@ -328,9 +359,9 @@ __global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *imag
         }
         // ---- bookkeeping in step order (both warps keep the same copy)
 #pragma unroll
-        for (int gg = 0; gg < 2; ++gg) {
+        for (int gg = 0; gg < W; ++gg) {
             if (gg < progress) {
-                const Vl2X x = gg == 0 ? x0 : x1;
+                const Vl2X x = xs[gg];
                 const bool acc = (x.flags & 1) != 0;
                 n_used8 += (x.flags >> 1) & 1;
                 nclamp += (x.flags >> 2) & 1;
@@ -360,7 +391,7 @@ __global__ void __launch_bounds__(64) k_run_vl2(Geo g, SiteRel rel, double *imag
     }
     {
         const int n_mut = g.o_sites + SITE_DOUBLES * N;
-        for (int qq = tid; qq < n_mut; qq += 64) gimg[qq] = img[qq];
+        for (int qq = tid; qq < n_mut; qq += NT) gimg[qq] = img[qq];
     }
     if (tid == 0) {
         s.step += done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.prod_acc += prod_acc;
