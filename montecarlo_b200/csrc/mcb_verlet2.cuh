@@ -357,23 +357,27 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
                 if (lane == 0) { energy[i] = esol; rowsum[i] = (dE + old_tot) - esol; }
             }
         }
-        // ---- bookkeeping in step order (both warps keep the same copy)
+        // ---- bookkeeping in step order: every warp tracks what steers the chain (accepted moves of the adaptation
+        //      window, list validity); the energy statistics only live on warp 0, whose lane 0 writes them back
 #pragma unroll
         for (int gg = 0; gg < W; ++gg) {
             if (gg < progress) {
                 const Vl2X x = xs[gg];
                 const bool acc = (x.flags & 1) != 0;
-                n_used8 += (x.flags >> 1) & 1;
-                nclamp += (x.flags >> 2) & 1;
-                sum_nn += (unsigned)x.nn;
-                s.last_delta = x.dE;
-                const bool in_prod = done + gg >= prod_from;        // selects instead of branches: adding 0.0 changes nothing
-                nsuc += acc; nacc += acc;
-                s.toteng += acc ? x.dE : 0.0;
-                s.production += acc && in_prod ? s.toteng : 0.0; prod_acc += acc && in_prod;
-                const double te = in_prod ? s.toteng : 0.0;
-                s.sum_e += te; s.sum_e2 = fma(te, te, s.sum_e2);
+                nacc += acc;
                 if (lists_on && acc && (x.flags & 8)) need_rebuild = true;   // the molecule now sits more than skin/2 from its build position
+                if (warp == 0) {
+                    n_used8 += (x.flags >> 1) & 1;
+                    nclamp += (x.flags >> 2) & 1;
+                    sum_nn += (unsigned)x.nn;
+                    s.last_delta = x.dE;
+                    const bool in_prod = done + gg >= prod_from;    // selects instead of branches: adding 0.0 changes nothing
+                    nsuc += acc;
+                    s.toteng += acc ? x.dE : 0.0;
+                    s.production += acc && in_prod ? s.toteng : 0.0; prod_acc += acc && in_prod;
+                    const double te = in_prod ? s.toteng : 0.0;
+                    s.sum_e += te; s.sum_e2 = fma(te, te, s.sum_e2);
+                }
             }
         }
         racc = nacc;
