@@ -369,6 +369,35 @@ def test_neighbour_lists_follow_state_changes(shipped, monkeypatch):
         _compare_chain(st, c, o.stats(), com3, hoek3, o)
 
 
+@pytest.mark.parametrize("width", ["2", "3", "4"])
+def test_steps_in_flight_edges(shipped, width, monkeypatch):
+    """k_run_vl2 with 2, 3 and 4 warps per chain on the 2x2x2 replica: launches shorter than a batch, an adaptation
+    window (nadj = 3) that is not a multiple of the batch, a production start in the middle of a batch, and a skin so
+    small that most steps fall back to the full scan on warp 0 - still the oracle's chain."""
+    box, system = shipped
+    b = boxio.replicate(box, 2)
+    s = _sys_for(system, b)
+    monkeypatch.setenv("MCB200_VL2_W", width)
+    for skin in ("2.0", "0.2"):
+        monkeypatch.setenv("MCB200_SKIN", skin)
+        eng = _engine(s, b.n, n_chains=2)
+        eng.set_state(b.com, b.hoek)
+        eng.set_mc_params(nadj=3, start_prod=50)
+        eng.seed(np.array([81, 82], dtype=np.uint64))
+        total = 0
+        for n in (1, 2, 3, 5, 7, 1, 64, 65, 300, 0, 11):
+            eng.run_steps(n)
+            total += n
+        st = eng.stats()
+        com, hoek = eng.get_state()
+        for c in range(2):
+            o = ol.OracleChain(s, b.com, b.hoek)
+            o.set_mc_params(nadj=3, start_prod=50)
+            o.total_energy()
+            o.run_steps_rng(total, ol.rng_seed(81 + c), trace=False)
+            _compare_chain(st, c, o.stats(), com, hoek, o)
+
+
 def test_neighbour_lists_default_size(shipped):
     """N = 810 (3x3x3 replica): k_run_vl by default; 1500 steps of two chains against the oracle."""
     box, system = shipped
