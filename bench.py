@@ -182,55 +182,45 @@ def run_reference_arm(args):
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
-def run_gpu_arm(args):
-    import torch
-    import torch.distributed as dist
-    from montecarlo_b200.engine import LJEngine, measure_fp64_peak
-    from montecarlo_b200 import boxio, partition
+def target_workload_name(chains, mc_steps):
+    return (f"configs[2] per-GPU share: 2x2x2 periodic replica of the shipped box (240 molecules, BOXL=15.5677371336, one "
+            f"11-atom solute), {chains} independent chains per GPU (seeds 1..), T=300K, {mc_steps} Metropolis steps per "
+            f"chain per launch")
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    inputs = ROOT / "tests" / "golden" / "inputs"
-    box = boxio.read_box(inputs / "box.txt")
-    system = boxio.load_system(box, inputs / "DMSO.txt", inputs / "param.txt", inputs / "par_solute.txt")
 
-    nch, S = args.chains, args.mc_steps
-    eng = LJEngine(system, box.n, n_chains=nch, device=local, lookahead=args.lookahead)
-    stream = torch.cuda.current_stream()
-    eng.set_stream(stream.cuda_stream)
-    # chains partitioned across ranks in contiguous blocks: rank r owns global chains [r*nch, (r+1)*nch)
-    seeds = partition.global_seeds(rank, world, nch * world)
+def oracle_check(eng, system, com, hoek, seed, nsteps, chain=0):
+    """One chain of the full-size batch against the C restatement on the same stream (checker only, untimed)."""
+    import oracle_lib as ol
+    st = eng.stats(chain, 1)
+    o = ol.OracleChain(system, com, hoek)
+    o.total_energy()
+    o.run_steps_rng(nsteps, ol.rng_seed(int(seed)), trace=False)
+    so = o.stats()
+    rel = abs(st["toteng"][0] - so["toteng"]) / abs(so["toteng"])
+    ok = bool(st["nsuc"][0] == so["nsuc"] and st["sitepairs"][0] == so["sitepairs"] and rel <= 1e-10)
+    return {"chain_seed": int(seed), "steps": int(nsteps), "accepted_equal": bool(st["nsuc"][0] == so["nsuc"]),
+            "sitepairs_equal": bool(st["sitepairs"][0] == so["sitepairs"]), "toteng_rel_err": float(rel), "ok": ok}
+
+
+def measure_leg(eng, system, box, nch, S, steps, warmup, seeds, stream, flush, barrier, torch):
+    """One workload on this rank: oracle check of the first chain, warm-up, `steps` event-timed launches with the state
+    resident in HBM (L2 flushed between them), then the same through the C ABI with host buffers."""
     com0 = np.ascontiguousarray(np.broadcast_to(box.com, (nch, box.n, 3)))
     hoek0 = np.ascontiguousarray(np.broadcast_to(box.hoek, (nch, box.n, 3)))
     eng.set_state(com0, hoek0)
     eng.seed(seeds)
     eng.total_energy()
-    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")   # > 126 MB L2
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- warm-up (also equilibrates the step sizes a little)
-    for _ in range(max(args.warmup, 3)):
+    n_check = min(S, 2000)
+    eng.run_steps(n_check, want_counts=False)
+    check = oracle_check(eng, system, box.com, box.hoek, seeds[0], n_check)
+    for _ in range(max(warmup, 3)):
         eng.run_steps(S, want_counts=False)
     torch.cuda.synchronize()
-
-    # ---- timed: K launches, state resident in HBM, L2 flushed between launches (outside the event pairs)
-    sampler = ClockSampler(local)
-    sampler.start()
     st0 = eng.stats()
     l0 = eng.launch_count
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     barrier()
-    for k in range(args.steps):
+    for k in range(steps):
         flush.zero_()
         ev[k][0].record(stream)
         eng.run_steps(S, want_counts=False)
@@ -239,19 +229,16 @@ def run_gpu_arm(args):
     kernel_ms = [a.elapsed_time(b) for a, b in ev]
     launches = eng.launch_count - l0
     st1 = eng.stats()
-    clocks = sampler.stop()
-    w_rank = float((st1["sitepairs"] - st0["sitepairs"]).sum())
-    moves_rank = float((st1["step"] - st0["step"]).sum())
-    t_rank = sum(kernel_ms) * 1e-3
-
+    out = {"check": check, "kernel_ms": kernel_ms, "launches": launches, "st1": st1,
+           "w": float((st1["sitepairs"] - st0["sitepairs"]).sum()), "moves": float((st1["step"] - st0["step"]).sum()),
+           "t": sum(kernel_ms) * 1e-3}
     # ---- end to end through the C ABI with host buffers: H2D of every chain's CoM/HOEK, K-step launch,
     #      D2H of the statistics and of the final coordinates (what the driver's dump/result writers read)
     com_h, hoek_h = eng.get_state()
-    e2e_ms = []
-    w_e2e = 0.0
-    h2d = com_h.nbytes + hoek_h.nbytes
-    d2h = com_h.nbytes + hoek_h.nbytes + nch * 128
-    for k in range(args.steps + 1):
+    e2e_ms, w_e2e = [], 0.0
+    out["h2d"] = com_h.nbytes + hoek_h.nbytes
+    out["d2h"] = com_h.nbytes + hoek_h.nbytes + nch * 128
+    for k in range(steps + 1):
         flush.zero_()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         s_before = eng.stats()["sitepairs"].sum()
@@ -266,80 +253,174 @@ def run_gpu_arm(args):
         if k > 0:
             e2e_ms.append(a.elapsed_time(b))
             w_e2e += float(st["sitepairs"].sum() - s_before)
-    t_e2e = sum(e2e_ms) * 1e-3
+    out.update(e2e_ms=e2e_ms, w_e2e=w_e2e, t_e2e=sum(e2e_ms) * 1e-3)
+    return out
 
-    # ---- whole-job aggregation: max time over ranks, sum of work; then the one collective of the path:
-    #      an all-reduce of the per-rank statistics vector (sum E, sum E^2, accepted, trials, site pairs)
-    t_all, t_e2e_all, w_all, moves_all, w_e2e_all = t_rank, t_e2e, w_rank, moves_rank, w_e2e
-    stats_ms = 0.0
+
+def run_gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    from montecarlo_b200.engine import LJEngine, measure_fp64_peak, comm_unique_id
+    from montecarlo_b200 import boxio, partition
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
     if world > 1:
-        tt = torch.tensor([t_rank, t_e2e], dtype=torch.float64, device="cuda")
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        t_all, t_e2e_all = tt.tolist()
-        sv = torch.tensor([w_rank, moves_rank, w_e2e], dtype=torch.float64, device="cuda")
-        dist.all_reduce(sv, op=dist.ReduceOp.SUM)
-        w_all, moves_all, w_e2e_all = sv.tolist()
-        # the path's one collective: all-reduce of the statistics vector + all-gather of per-chain final energies
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    inputs = ROOT / "tests" / "golden" / "inputs"
+    box = boxio.read_box(inputs / "box.txt")
+    system = boxio.load_system(box, inputs / "DMSO.txt", inputs / "param.txt", inputs / "par_solute.txt")
+    stream = torch.cuda.current_stream()
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
         torch.cuda.synchronize()
-        a.record()
-        global_stats = partition.reduce_stats(st1, device="cuda")
-        final_e = partition.gather_per_chain(st1["toteng"], nch * world, device="cuda")
-        b.record()
-        torch.cuda.synchronize()
-        stats_ms = a.elapsed_time(b)
-        assert final_e.shape[0] == nch * world and global_stats["step"] == st1["step"].sum() * world
+
+    def join_comm(eng, n_total):
+        """The job's NCCL communicator lives inside libmcb200.so; torch.distributed only carries the 128-byte id."""
+        if world == 1:
+            return
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        eng.comm_init(world, rank, bytes(idt.cpu().numpy().tobytes()), n_total)
+
+    sampler = ClockSampler(local)
+    sampler.start()
+    # ---- leg 1 = the headline: BASELINE configs[1], chains partitioned over ranks in contiguous blocks
+    nch, S = args.chains, args.mc_steps
+    eng = LJEngine(system, box.n, n_chains=nch, device=local, lookahead=args.lookahead)
+    eng.set_stream(stream.cuda_stream)
+    seeds = partition.global_seeds(rank, world, nch * world)
+    join_comm(eng, nch * world)
+    m1 = measure_leg(eng, system, box, nch, S, args.steps, args.warmup, seeds, stream, flush, barrier, torch)
+    # the path's one collective, inside the product: all-reduce of the statistics + all-gather of per-chain finals
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    a.record(stream)
+    gstats = eng.reduce_stats()
+    finals = eng.gather_chains()
+    b.record(stream)
+    torch.cuda.synchronize()
+    stats_ms = a.elapsed_time(b)
+    assert finals["toteng"].shape[0] == nch * world and int(gstats["n_chains"][0]) == nch * world
+    assert int(gstats["step"][0]) == int(m1["st1"]["step"].sum()) * world
+    assert np.array_equal(finals["toteng"][rank * nch:(rank + 1) * nch], m1["st1"]["toteng"])
+    eng.close()
+
+    # ---- leg 2 = the box north_star's target is quoted on: 2x2x2 replica, configs[2]'s per-GPU share of chains
+    m2 = None
+    if args.target_chains > 0:
+        b2 = boxio.replicate(box, 2)
+        sys2 = boxio.System(**{**system.__dict__, "boxl": b2.boxl, "solute": b2.solute})
+        nch2, S2 = args.target_chains, args.target_mc_steps
+        eng2 = LJEngine(sys2, b2.n, n_chains=nch2, device=local)
+        eng2.set_stream(stream.cuda_stream)
+        seeds2 = partition.global_seeds(rank, world, nch2 * world)
+        m2 = measure_leg(eng2, sys2, b2, nch2, S2, args.steps, args.warmup, seeds2, stream, flush, barrier, torch)
+        eng2.close()
+    clocks = sampler.stop()
+
+    # ---- whole-job aggregation: max time over ranks, sum of work (torch.distributed = plumbing for the bench's own numbers)
+    def aggregate(m):
+        t, te, w, mv, we = m["t"], m["t_e2e"], m["w"], m["moves"], m["w_e2e"]
+        ok = 1.0 if m["check"]["ok"] else 0.0
+        if world > 1:
+            tt = torch.tensor([t, te, -ok], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            t, te, ok = tt[0].item(), tt[1].item(), -tt[2].item()
+            sv = torch.tensor([w, mv, we], dtype=torch.float64, device="cuda")
+            dist.all_reduce(sv, op=dist.ReduceOp.SUM)
+            w, mv, we = sv.tolist()
+        return t, te, w, mv, we, ok == 1.0
+
+    agg1 = aggregate(m1)
+    agg2 = aggregate(m2) if m2 else None
 
     if rank == 0:
         peak_tf = measure_fp64_peak(local, 150.0)
-        value = w_all / t_all
-        w_launch = w_rank / max(launches, 1)
-        t_launch = t_rank / max(launches, 1)
-        achieved_tf = w_launch * FLOP_PER_SITEPAIR / t_launch / 1e12
         peaks = {}
         try:
             peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
         except (OSError, ValueError):
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
-        # algorithmic bytes per launch: every chain's image is read once and its mutable part written once
-        g_image = (19 * 32 + 12 * 3 + 4 * 48 + 30 * 31) * 8
-        alg_bytes = nch * (g_image + (7 * 32 + 12 * 30 + 30 * 31) * 8 + 2 * 216)
-        traffic = None
-        tp = ROOT / "profiles" / "traffic_r01.json"
+        traffic = {}
+        tp = ROOT / "profiles" / "traffic_r02.json"
         if tp.exists():
             try:
-                traffic = json.loads(tp.read_text()).get("dram_bytes_per_launch")
+                traffic = json.loads(tp.read_text())
             except ValueError:
                 pass
+
+        def roofline(m, kernel, alg_bytes, tkey):
+            w_launch = m["w"] / max(m["launches"], 1)
+            t_launch = m["t"] / max(m["launches"], 1)
+            achieved_tf = w_launch * FLOP_PER_SITEPAIR / t_launch / 1e12
+            tr = traffic.get(tkey, {})
+            return {"bound": "fp64", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
+                    "traffic": tr.get("dram_bytes_per_launch"), "kernel": kernel, "flop_per_site_pair": FLOP_PER_SITEPAIR,
+                    "site_pairs_per_launch": w_launch, "kernel_ms": 1e3 * t_launch,
+                    "dram_bytes_per_move": tr.get("dram_bytes_per_move"), "l2_bytes_per_move": tr.get("l2_bytes_per_move"),
+                    "traffic_source": tr.get("source"),
+                    "peak_source": "measured live: mcb_measure_fp64_peak (independent DFMA chains, all SMs, loop-invariant "
+                                   "multiplier and addend: 98 % of the nominal 148 SM x 64 DFMA/clk x 1.965 GHz); "
+                                   "MEASURED_PEAKS.json has no fp64 entry",
+                    "hbm": {"achieved": alg_bytes / t_launch / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                            "frac": alg_bytes / t_launch / 1e9 / hbm_peak, "algorithmic_bytes_per_launch": alg_bytes,
+                            "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}}
+
+        t_all, t_e2e_all, w_all, moves_all, w_e2e_all, ok1 = agg1
+        value = w_all / t_all
+        # algorithmic bytes per launch: every chain's image is read once and its mutable part written once
+        g_image = (19 * 32 + 12 * 3 + 4 * 48 + 30 * 31) * 8
+        alg1 = nch * (g_image + (7 * 32 + 12 * 30 + 30 * 31) * 8 + 2 * 216)
+        st1 = m1["st1"]
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": 1e3 * t_all / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(nch, S), "chains_per_gpu": nch, "mc_steps_per_launch": S,
-                       "parallelism": f"chains x{world} (no data-path collective; one all-reduce of statistics at the end)",
+                       "parallelism": f"chains x{world} (no data-path collective; one NCCL all-reduce + all-gather of statistics "
+                                      f"at the end, inside libmcb200.so: mcb_reduce_stats / mcb_gather_chains)",
                        "l2": "flushed between timed launches (256 MiB memset outside the event pairs)",
                        "uniforms": "built-in counter stream (mcb_seed_chains), seed = global chain index + 1"},
             "trial_moves_per_s": moves_all / t_all,
             "sitepairs_per_move": w_all / max(moves_all, 1.0),
             "acceptance": float(st1["nsuc"].sum() / max(st1["step"].sum(), 1)),
-            "e2e": {"value": w_e2e_all / t_e2e_all, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": 1e3 * t_e2e_all / max(len(e2e_ms), 1),
+            "oracle_check": {**m1["check"], "all_ranks_ok": ok1},
+            "e2e": {"value": w_e2e_all / t_e2e_all, "unit": UNIT, "h2d_bytes_per_step": m1["h2d"], "d2h_bytes_per_step": m1["d2h"],
+                    "ms_per_step": 1e3 * t_e2e_all / max(len(m1["e2e_ms"]), 1),
                     "path": "mcb_set_chain_state -> mcb_run_steps -> mcb_get_stats + mcb_get_chain_state (host numpy buffers)"},
-            "gpu_launches": int(launches),
+            "gpu_launches": int(m1["launches"]),
             "clocks": clocks,
-            "roofline": {"bound": "fp64", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                         "frac": achieved_tf / peak_tf, "traffic": traffic,
-                         "kernel": "k_run_spec", "flop_per_site_pair": FLOP_PER_SITEPAIR,
-                         "site_pairs_per_launch": w_launch, "kernel_ms": 1e3 * t_launch,
-                         "peak_source": "measured live: mcb_measure_fp64_peak (independent DFMA chains, all SMs); "
-                                        "MEASURED_PEAKS.json has no fp64 entry",
-                         "hbm": {"achieved": alg_bytes / t_launch / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                                 "frac": alg_bytes / t_launch / 1e9 / hbm_peak, "algorithmic_bytes_per_launch": alg_bytes,
-                                 "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}},
+            "roofline": roofline(m1, "k_run_spec", alg1, "k_run_spec"),
+            "stats_collective_ms": stats_ms,
         }
-        if world > 1:
-            line["stats_allreduce_ms"] = stats_ms
+        if m2:
+            t2, te2, w2, mv2, we2, ok2 = agg2
+            n2 = 240
+            # per launch: the chain image (coordinates, site cache, tables) in and its mutable part out; the pair
+            # matrix is read once for the row sums (N x MS doubles) and written only where it changes
+            alg2 = args.target_chains * ((7 * n2 + 12 * (n2 + 3) + 4 * 48 + n2 * (n2 + 1)) * 8 + (7 * n2 + 12 * n2) * 8 + 2 * 216)
+            line["target_box"] = {
+                "workload": target_workload_name(args.target_chains, args.target_mc_steps),
+                "chains_per_gpu": args.target_chains, "mc_steps_per_launch": args.target_mc_steps,
+                "value": w2 / t2, "unit": UNIT, "trial_moves_per_s": mv2 / t2, "sitepairs_per_move": w2 / max(mv2, 1.0),
+                "ms_per_step": 1e3 * t2 / args.steps, "gpu_launches": int(m2["launches"]),
+                "acceptance": float(m2["st1"]["nsuc"].sum() / max(m2["st1"]["step"].sum(), 1)),
+                "oracle_check": {**m2["check"], "all_ranks_ok": ok2},
+                "e2e": {"value": we2 / te2, "unit": UNIT, "h2d_bytes_per_step": m2["h2d"], "d2h_bytes_per_step": m2["d2h"],
+                        "ms_per_step": 1e3 * te2 / max(len(m2["e2e_ms"]), 1)},
+                "roofline": roofline(m2, args.target_kernel_name, alg2, "target_box"),
+            }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline()
         print(json.dumps(line))
@@ -357,6 +438,9 @@ def main():
     ap.add_argument("--chains", type=int, default=1024, help="chains per GPU")
     ap.add_argument("--mc-steps", type=int, default=5000, help="Metropolis steps per chain per launch")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--target-chains", type=int, default=512, help="chains per GPU of the second leg (2x2x2 replica, N = 240); 0 = skip")
+    ap.add_argument("--target-mc-steps", type=int, default=4000, help="Metropolis steps per chain per launch of the second leg")
+    ap.add_argument("--target-kernel-name", default="k_run_vl2", help=argparse.SUPPRESS)
     ap.add_argument("--lookahead", type=int, default=0, help="speculative look-ahead depth of mcb_run_steps (0 = library default)")
     args = ap.parse_args()
     # stdout carries the ONE JSON line and nothing else: libraries that write to file descriptor 1 (NCCL prints a

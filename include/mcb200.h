@@ -109,7 +109,8 @@ int mcb_total_energy(mcb_t *h, int chain0, int nchains, double *toteng, double *
 /* replaces: the `solventsolvent` dump (MonteCarlo.F90:372-376): ss [n_mol][n_mol], energy [n_mol] */
 int mcb_get_matrix(mcb_t *h, int chain, double *ss, double *energy);
 /* replaces: CALL calculateLJ(I) read-only (MonteCarlo.F90:792-828): row I of the pair matrix recomputed from
- * the current coordinates with I as MOL1, and ENERGY(I).  i is 1-based. */
+ * the current coordinates with I as MOL1, and ENERGY(I).  i is 1-based.  Argument error while a trial from
+ * mcb_trial_delta waits for its mcb_commit (both use the chain's work area). */
 int mcb_row_energy(mcb_t *h, int chain, int i, double *ss_row, double *e_i);
 
 /* ---- single-step mode: the driver keeps MCINIT / METROPOLIS (RNG, accept/reject) ------------------- */
@@ -127,8 +128,10 @@ int mcb_set_mc_params(mcb_t *h, int chain0, int nchains, const mcb_mc_params *p,
 /* Uniform stream used when mcb_run_steps gets no buffer: counter-based and random-access,
  *   G = 0x9E3779B97F4A7C15, mix = splitmix64's finaliser, key = mix(seed + G),
  *   u(n) = (mix(key + (n+1)*G) >> 11) * 2^-53 in [0,1);
- * Metropolis step s (0-based, counted over the chain's life: mcb_chain_stats.step) reads u(8s) .. u(8s+6) for
- * MCINIT and u(8s+7) if METROPOLIS draws.  (The reference's own RNG is the compiler's RANDOM_NUMBER seeded from
+ * Metropolis step s reads u(8s) .. u(8s+6) for MCINIT and u(8s+7) if METROPOLIS draws, where s counts every step
+ * mcb_run_steps has made for the chain since it was seeded (0-based).  mcb_reset_stats does NOT rewind it: an
+ * equilibrate / reset / production sequence goes on in the stream, it never replays the equilibration's numbers.
+ * Only mcb_seed_chains puts s back to 0.  (The reference's own RNG is the compiler's RANDOM_NUMBER seeded from
  * /dev/urandom, MC_lib/randgen.f90:15-40: there is no reference stream to reproduce; a driver that wants its
  * own stream passes a buffer.) */
 int mcb_seed_chains(mcb_t *h, int chain0, int nchains, const uint64_t *seeds);
@@ -141,8 +144,43 @@ int mcb_seed_chains(mcb_t *h, int chain0, int nchains, const uint64_t *seeds);
 int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, int64_t cap, int64_t *consumed,
                   int64_t *steps_done);
 int mcb_get_stats(mcb_t *h, int chain0, int nchains, mcb_chain_stats *out);
-/* zero the counters (step, nsuc, production, ...) but keep coordinates, energies and step sizes */
+/* zero the counters (step, nsuc, production, ...) but keep coordinates, energies, step sizes and the position in
+ * the built-in uniform stream */
 int mcb_reset_stats(mcb_t *h, int chain0, int nchains);
+
+/* ---- end of run: one collective over the GPUs of the job ---------------------------------------------- */
+/* replaces: the way the reference combines its independent runs - separate processes whose logs PostProcess scrapes
+ * afterwards (PostProcess/PostProcess.F90:202-256 RECON / READLOG).  The chains of a job are spread over the GPUs in
+ * contiguous blocks - rank r of nranks holds n_total/nranks chains, the first n_total % nranks ranks one more - one
+ * handle (and one host process or thread) per GPU, nothing is exchanged while sampling, and the run ends with ONE
+ * NCCL all-reduce (mcb_reduce_stats) and ONE all-gather (mcb_gather_chains) over NVLink.  NCCL is bound at run time
+ * (libnccl.so.2); without it these calls fail with a message and everything else still works. */
+#define MCB_COMM_ID_BYTES 128
+/* rank 0 calls this and hands the 128 bytes to the other ranks by its own means (MPI_Bcast, a file, a socket) */
+int mcb_comm_get_unique_id(char id[MCB_COMM_ID_BYTES]);
+/* collective over all ranks: joins the communicator on the handle's GPU; h must hold exactly rank's block */
+int mcb_comm_init(mcb_t *h, int nranks, int rank, const char id[MCB_COMM_ID_BYTES], int64_t n_total_chains);
+/* the same with a communicator the host already has (an ncclComm_t, e.g. from its MPI+NCCL set-up); not destroyed here */
+int mcb_comm_attach(mcb_t *h, void *nccl_comm, int nranks, int rank, int64_t n_total_chains);
+int mcb_comm_destroy(mcb_t *h);
+
+/* Sums over all chains of a group, over all ranks: what the production average (MonteCarlo.F90:555-560) and the
+ * acceptance printed at the end of a run need, per run in the reference, per group of chains here. */
+typedef struct {
+    double sum_e, sum_e2;   /* sums of mcb_chain_stats.sum_e / sum_e2 */
+    double production;      /* sum of PRODUCTION */
+    double sum_toteng;      /* sum of the final TOTENG */
+    int64_t n_stat, prod_acc, nsuc, step, sitepairs, n_clamped, uniforms_used;
+    int64_t n_chains;       /* chains in the group */
+} mcb_global_stats;
+/* Collective.  Group g = global chains [g*chains_per_group, (g+1)*chains_per_group) (BASELINE config 4: one group per
+ * dihedral angle); chains_per_group <= 0: one group with everything.  n_groups = ceil(n_total / chains_per_group) is
+ * checked.  Every rank receives every group.  Without mcb_comm_init the handle's own chains are summed (one rank). */
+int mcb_reduce_stats(mcb_t *h, int64_t chains_per_group, mcb_global_stats *out, int n_groups);
+/* Collective.  out[n_total_chains][4] in global chain order: final TOTENG, mean energy sum_e/n_stat, acceptance
+ * nsuc/step, production mean PRODUCTION/PROD_ACC (0 where the divisor is 0) - what PostProcess reads from each run's
+ * log (' Energy:' lines, PostProcess.F90:229-256). */
+int mcb_gather_chains(mcb_t *h, double *out, int64_t n_total_chains);
 
 /* ---- for hosts that must not allocate ---------------------------------------------------------------- */
 /* No counterpart in the reference (which never touches a GPU).  Same result as mcb_total_energy, for callers

@@ -17,7 +17,7 @@ SOURCES = [PKG / "csrc" / "mcb200.cu"]
 HEADERS = [PKG / "csrc" / "mcb_device.cuh", PKG / "csrc" / "mcb_kernels.cuh", PKG / "csrc" / "mcb_verlet.cuh", PKG / "csrc" / "mcb_verlet2.cuh", PKG / "csrc" / "mcb_cells.cuh", ROOT / "include" / "mcb200.h"]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "-shared", "-Xcompiler", "-fPIC"]
+              "-shared", "-Xcompiler", "-fPIC", "-ldl"]
 
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int)
@@ -48,6 +48,14 @@ class McbChainStats(C.Structure):
                 ("n_stat", C.c_int64)]
 
 
+class McbGlobalStats(C.Structure):
+    _fields_ = [("sum_e", C.c_double), ("sum_e2", C.c_double), ("production", C.c_double), ("sum_toteng", C.c_double),
+                ("n_stat", C.c_int64), ("prod_acc", C.c_int64), ("nsuc", C.c_int64), ("step", C.c_int64),
+                ("sitepairs", C.c_int64), ("n_clamped", C.c_int64), ("uniforms_used", C.c_int64), ("n_chains", C.c_int64)]
+
+
+COMM_ID_BYTES = 128
+
 # every symbol include/mcb200.h declares: name -> (restype, argtypes)
 SIGNATURES = {
     "mcb_create": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(McbParams)]),
@@ -69,6 +77,12 @@ SIGNATURES = {
     "mcb_get_stats": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(McbChainStats)]),
     "mcb_reset_stats": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "mcb_measure_fp64_peak": (C.c_int, [C.c_int, C.c_double, _dp]),
+    "mcb_comm_get_unique_id": (C.c_int, [C.c_char_p]),
+    "mcb_comm_init": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_int64]),
+    "mcb_comm_attach": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int64]),
+    "mcb_comm_destroy": (C.c_int, [C.c_void_p]),
+    "mcb_reduce_stats": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(McbGlobalStats), C.c_int]),
+    "mcb_gather_chains": (C.c_int, [C.c_void_p, _dp, C.c_int64]),
     "mcb_box_energy_noalloc": (C.c_int, [C.POINTER(McbParams), C.c_void_p, C.c_void_p, _dp, _dp, C.c_void_p, C.c_void_p,
                                          C.c_char_p, C.c_size_t]),
 }

@@ -42,6 +42,23 @@ class Box:
         return int(self.solute.shape[0])
 
 
+def _dihedral_line(line: str) -> tuple[int, int, float]:
+    """One dihedral line as the reference reads it: fixed columns `(I3, 1X, I3, 1X, F10.6)` (MonteCarlo.F90:1123), so
+    fields that touch (`12 13-90.000000`) still parse; blanks inside a numeric field are ignored, an F10.6 field
+    without a decimal point has its last six digits taken as decimals, and a rotation of 0 means "use the global
+    one", stored as -1 (:1124).  (The clip to DROTSOLU, :1125, needs the driver's config and stays with the driver.)"""
+    line = line.rstrip("\n").ljust(18)
+    a, b, r = line[0:3].replace(" ", ""), line[4:7].replace(" ", ""), line[8:18].replace(" ", "")
+    ia, ib = (int(a) if a else 0), (int(b) if b else 0)
+    if not r:
+        rot = 0.0
+    elif any(ch in r for ch in ".eEdD"):
+        rot = _f(r)
+    else:
+        rot = int(r) / 1.0e6
+    return ia, ib, (-1.0 if rot == 0.0 else rot)
+
+
 def read_box(path: str | Path) -> Box:
     """Reads the current box format (reference MonteCarlo.F90:1078-1128)."""
     lines = Path(path).read_text().splitlines()
@@ -71,9 +88,8 @@ def read_box(path: str | Path) -> Box:
         box.sol_sym, box.solute = syms, np.array(xyz, dtype=np.float64).reshape(nsol, 3)
         box.e_sol = _f(lines[p].split()[0]); p += 1
         ndih = int(lines[p].split()[0]); p += 1
-        for i in range(ndih):  # (I3,1X,I3,1X,F10.6)
-            t = lines[p + i].split()
-            box.dihedrals.append((int(t[0]), int(t[1]), _f(t[2])))
+        for i in range(ndih):
+            box.dihedrals.append(_dihedral_line(lines[p + i]))
     return box
 
 

@@ -20,6 +20,8 @@
 
 using namespace mcb;
 
+struct mcb_comm_state;   // NCCL side of a handle, defined with the collective at the end of this file
+
 struct mcb_handle {
     mcb_params prm{};
     Geo g{};
@@ -32,6 +34,8 @@ struct mcb_handle {
     int ncell = 0;
     VerletBufs vl{};        // neighbour lists of k_run_vl (large boxes); idx == nullptr: not in use
     int vl2_w = 0;          // warps per chain of k_run_vl2: 0 not chosen yet, -1 does not fit
+    bool no_vl2 = false;    // MCB200_NO_VL2 (read once, at mcb_create)
+    bool trial_pending = false;   // mcb_trial_delta has parked a trial that mcb_commit has not resolved yet
     cudaStream_t stream = nullptr;
     double *images = nullptr, *matg = nullptr, *work = nullptr;
     ChainCtl *ctl = nullptr;
@@ -44,10 +48,14 @@ struct mcb_handle {
     long long launches = 0;
     size_t smem_bytes = 0, smem_spec_bytes = 0;
     int lookahead = 4, spec_w = 1, spec_gl = 32;
+    mcb_comm_state *comm = nullptr;   // NCCL communicator of the end-of-run collective (mcb_comm_init), or none
     std::string err;
 };
 
-static std::string g_create_err;
+static void comm_free(mcb_handle *h);
+
+// error text of a failed mcb_create: one per host thread, so that concurrent creates do not write the same string
+static thread_local std::string g_create_err;
 
 #define CK(h, call)                                                                                   \
     do {                                                                                              \
@@ -132,6 +140,7 @@ extern "C" int mcb_destroy(mcb_t *h)
 {
     if (!h) return 0;
     cudaSetDevice(h->device);
+    comm_free(h);
     cudaFree(h->images); cudaFree(h->matg); cudaFree(h->work); cudaFree(h->ctl);
     cudaFree(h->d_rsolv); cudaFree(h->d_vec); cudaFree(h->d_out); cudaFree(h->d_ll); cudaFree(h->d_acc);
     cudaFree(h->d_ubuf);
@@ -233,6 +242,7 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
     // N = 810: 1.2e10 vs 3e9; profiles/other_configs_r01.txt)
     int vl_min_n = 33;
     if (const char *mn = getenv("MCB200_VERLET_MIN_N")) vl_min_n = atoi(mn);   // tuning only
+    h->no_vl2 = getenv("MCB200_NO_VL2") != nullptr;
     if (!h->energy_only && !g.mat_in_image && g.N >= vl_min_n && g.N > 32 && g.N < 65536 && h->spec_w == 1 && h->spec_gl == 32 && !getenv("MCB200_NO_VERLET")) {
         // large box, one step per warp: neighbour lists for k_run_vl (mcb_verlet.cuh)
         h->vl.skin = 2.0;
@@ -511,6 +521,7 @@ extern "C" int mcb_trial_delta(mcb_t *h, int nchains, const int *rsolv, const do
     CK(h, cudaMemcpyAsync(d_com, new_com, sizeof(double) * 3 * nchains, cudaMemcpyHostToDevice, h->stream));
     CK(h, cudaMemcpyAsync(d_hoek, new_hoek, sizeof(double) * 3 * nchains, cudaMemcpyHostToDevice, h->stream));
     if (int rc = launch_trial(h, 0, nchains, 0)) return rc;
+    h->trial_pending = true;
     if (d_e) CK(h, cudaMemcpyAsync(d_e, h->d_out, sizeof(double) * nchains, cudaMemcpyDeviceToHost, h->stream));
     if (e_new) CK(h, cudaMemcpyAsync(e_new, h->d_out + h->n_chains, sizeof(double) * nchains, cudaMemcpyDeviceToHost, h->stream));
     CK(h, cudaStreamSynchronize(h->stream));
@@ -523,6 +534,7 @@ extern "C" int mcb_commit(mcb_t *h, int nchains, const unsigned char *accept)
     if (!accept) return arg_err(h, "mcb_commit: null array");
     if (h->energy_only) return arg_err(h, "mcb_commit: this handle is in energy-only mode");
     h->vl.trust = 0;
+    h->trial_pending = false;
     CK(h, cudaSetDevice(h->device));
     CK(h, cudaMemcpyAsync(h->d_acc, accept, nchains, cudaMemcpyHostToDevice, h->stream));
     k_commit<<<nchains, 32, 0, h->stream>>>(h->g, h->images, h->matg, h->work, h->ctl, h->d_acc);
@@ -537,16 +549,18 @@ extern "C" int mcb_row_energy(mcb_t *h, int chain, int i, double *ss_row, double
     if (int rc = check_range(h, chain, 1)) return rc;
     if (i < 1 || i > h->g.N) return arg_err(h, "mcb_row_energy: i outside 1..n_mol");
     if (h->energy_only) return arg_err(h, "mcb_row_energy: this handle is in energy-only mode");
+    // the read-only evaluation uses the same per-chain work area as a parked trial and would drop it
+    if (h->trial_pending) return arg_err(h, "mcb_row_energy: a trial from mcb_trial_delta is pending; call mcb_commit first");
     CK(h, cudaSetDevice(h->device));
     if (int rc = ensure_prepared(h)) return rc;
     const Geo &g = h->g;
-    // a read-only "trial" that moves molecule i onto itself: new coordinates = current coordinates
-    std::vector<double> com((size_t)g.N * 3), hoek((size_t)g.N * 3);
-    if (int rc = mcb_get_chain_state(h, chain, 1, com.data(), hoek.data())) return rc;
+    // a read-only "trial" that moves molecule i onto itself: new coordinates = current coordinates, copied on the
+    // device from the chain's image (six values, one per SoA plane)
     double *d_com = h->d_vec, *d_hoek = h->d_vec + 3 * (size_t)h->n_chains;
+    const double *img = h->images + (size_t)chain * g.image_doubles;
     CK(h, cudaMemcpyAsync(h->d_rsolv, &i, sizeof(int), cudaMemcpyHostToDevice, h->stream));
-    CK(h, cudaMemcpyAsync(d_com, &com[(size_t)(i - 1) * 3], sizeof(double) * 3, cudaMemcpyHostToDevice, h->stream));
-    CK(h, cudaMemcpyAsync(d_hoek, &hoek[(size_t)(i - 1) * 3], sizeof(double) * 3, cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaMemcpy2DAsync(d_com, 8, img + g.o_com + (i - 1), (size_t)g.Np * 8, 8, 3, cudaMemcpyDeviceToDevice, h->stream));
+    CK(h, cudaMemcpy2DAsync(d_hoek, 8, img + g.o_hoek + (i - 1), (size_t)g.Np * 8, 8, 3, cudaMemcpyDeviceToDevice, h->stream));
     if (int rc = launch_trial(h, chain, 1, 1)) return rc;
     const double *wk = h->work + (size_t)chain * g.work_doubles;
     if (ss_row) CK(h, cudaMemcpyAsync(ss_row, wk + g.o_newrow, sizeof(double) * g.N, cudaMemcpyDeviceToHost, h->stream));
@@ -731,7 +745,7 @@ extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, i
     if (uniforms) { if (h->coul) launch_run_ubuf<true>(h, nsteps, cap, d_consumed, d_steps); else launch_run_ubuf<false>(h, nsteps, cap, d_consumed, d_steps); }
     else {
         CK(h, cudaMemsetAsync(d_consumed, 0, sizeof(long long) * nc, h->stream));
-        if (h->vl.idx && !h->vl2_w && !getenv("MCB200_NO_VL2")) h->vl2_w = pick_vl2_width(h);
+        if (h->vl.idx && !h->vl2_w && !h->no_vl2) h->vl2_w = pick_vl2_width(h);
         if (h->vl.idx && h->vl2_w > 0) {
             // W warps per chain, W consecutive steps in flight (mcb_verlet2.cuh)
             switch (h->vl2_w) {
@@ -967,10 +981,19 @@ extern "C" int mcb_box_energy_noalloc(const mcb_params *p, const double *d_com, 
         na_msg(errbuf, errbuf_len, "mcb_box_energy_noalloc: bad parameter (1 <= n_sites <= 4; boxl, cutoff > 0)");
         return 1;
     }
-    int dev = 0;
-    cudaError_t e = p->device >= 0 ? cudaSetDevice(p->device) : cudaSuccess;
+    // p->device >= 0 selects that GPU for this call only: the caller's current device is put back before returning
+    int dev = 0, caller_dev = -1;
+    cudaError_t e = cudaGetDevice(&caller_dev);
+    if (e == cudaSuccess && p->device >= 0 && p->device != caller_dev) e = cudaSetDevice(p->device);
     if (e == cudaSuccess) e = cudaGetDevice(&dev);
+    struct Restore { int d; bool on; ~Restore() { if (on) cudaSetDevice(d); } } restore{caller_dev, e == cudaSuccess && dev != caller_dev};
     if (e != cudaSuccess || dev < 0 || dev >= NA_MAX_DEVICES) { na_msg(errbuf, errbuf_len, e != cudaSuccess ? cudaGetErrorString(e) : "device ordinal too large"); return -(int)(e != cudaSuccess ? e : cudaErrorInvalidDevice); }
+    // an error some earlier call of the host left behind is the host's: report it as such instead of as a launch failure
+    e = cudaPeekAtLastError();
+    if (e != cudaSuccess) {
+        if (errbuf && errbuf_len) snprintf(errbuf, errbuf_len, "mcb_box_energy_noalloc: the CUDA context already holds an error from an earlier call (%s); nothing was launched", cudaGetErrorString(e));
+        return -(int)e;
+    }
     NaScratch *sc = nullptr;
     {   // set-up, once per device, with that device current: resolve the device address of the scratch symbol
         std::lock_guard<std::mutex> lock(g_na_mutex);
@@ -1005,5 +1028,272 @@ extern "C" int mcb_box_energy_noalloc(const mcb_params *p, const double *d_com, 
     k_na_reduce<<<1, BIG_TILE, 0, st>>>(sc, blocks, tiles, d_out);
     e = cudaGetLastError();
     if (e != cudaSuccess) { na_msg(errbuf, errbuf_len, cudaGetErrorString(e)); return -(int)e; }
+    return 0;
+}
+
+// ================================================================================================
+// End-of-run collective: mcb_comm_* / mcb_reduce_stats / mcb_gather_chains.
+//
+// The reference runs its independent chains as separate OS processes and combines them afterwards by scraping
+// their logs (PostProcess/PostProcess.F90:202-256, RECON and READLOG).  Here the chains of one job are spread over
+// the GPUs of a box in contiguous blocks (one handle per GPU, nothing exchanged while sampling) and combined
+// by ONE NCCL all-reduce of a small statistics vector and ONE all-gather of four numbers per chain, both over
+// NVLink.  NCCL is bound at run time (dlopen of libnccl.so.2; the copy a host such as PyTorch has already loaded is
+// reused), so single-GPU users of the library do not need it installed.
+// ================================================================================================
+#include <dlfcn.h>
+#include <nccl.h>
+
+namespace {
+
+struct NcclApi {
+    void *lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    ncclResult_t (*GetVersion)(int *) = nullptr;
+    std::string err;
+};
+
+NcclApi g_nccl;
+std::mutex g_nccl_mutex;
+
+// nullptr on success, else why NCCL could not be bound
+const char *nccl_bind()
+{
+    std::lock_guard<std::mutex> lock(g_nccl_mutex);
+    NcclApi &n = g_nccl;
+    if (n.lib) return nullptr;
+    if (!n.err.empty()) return n.err.c_str();
+    void *lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);      // the copy the host process already uses, if any
+    if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) { n.err = std::string("NCCL not found (dlopen libnccl.so.2): ") + dlerror(); return n.err.c_str(); }
+    bool ok = true;
+    auto sym = [&](const char *name) { void *p = dlsym(lib, name); if (!p) { ok = false; n.err = std::string("NCCL symbol missing: ") + name; } return p; };
+    n.GetUniqueId = reinterpret_cast<decltype(n.GetUniqueId)>(sym("ncclGetUniqueId"));
+    n.CommInitRank = reinterpret_cast<decltype(n.CommInitRank)>(sym("ncclCommInitRank"));
+    n.CommDestroy = reinterpret_cast<decltype(n.CommDestroy)>(sym("ncclCommDestroy"));
+    n.AllReduce = reinterpret_cast<decltype(n.AllReduce)>(sym("ncclAllReduce"));
+    n.AllGather = reinterpret_cast<decltype(n.AllGather)>(sym("ncclAllGather"));
+    n.GroupStart = reinterpret_cast<decltype(n.GroupStart)>(sym("ncclGroupStart"));
+    n.GroupEnd = reinterpret_cast<decltype(n.GroupEnd)>(sym("ncclGroupEnd"));
+    n.GetErrorString = reinterpret_cast<decltype(n.GetErrorString)>(sym("ncclGetErrorString"));
+    n.GetVersion = reinterpret_cast<decltype(n.GetVersion)>(sym("ncclGetVersion"));
+    if (!ok) return n.err.c_str();
+    n.lib = lib;
+    return nullptr;
+}
+
+constexpr int GS_D = 4, GS_I = 8;   // doubles and 64-bit counters of one mcb_global_stats
+
+// Per-group partial sums over this rank's chains, one block per group, fixed order (no fp64 atomics): group g holds
+// the global chains [g * per_group, (g + 1) * per_group); this rank owns [offset, offset + n_local).
+__global__ void __launch_bounds__(128) k_stats_groups(const ChainCtl *ctl, int n_local, long long offset, long long per_group,
+                                                      double *out_d, long long *out_i)
+{
+    __shared__ double red[BIG_TILE];
+    const long long g0 = (long long)blockIdx.x * per_group, g1 = g0 + per_group;
+    const long long lo = max(g0, offset) - offset, hi = min(g1, offset + (long long)n_local) - offset;
+    double d[GS_D] = {0, 0, 0, 0}, c[GS_I] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (long long k = lo + threadIdx.x; k < hi; k += BIG_TILE) {
+        const ChainCtl &s = ctl[k];
+        d[0] += s.sum_e; d[1] += s.sum_e2; d[2] += s.production; d[3] += s.toteng;
+        c[0] += (double)s.nstat; c[1] += (double)s.prod_acc; c[2] += (double)s.nsuc; c[3] += (double)s.step;
+        c[4] += (double)s.sitepairs; c[5] += (double)s.nclamp; c[6] += (double)s.uused; c[7] += 1.0;
+    }
+    // (the counters are summed as doubles inside the block: exact below 2^53, then stored as integers)
+    for (int q = 0; q < GS_D; ++q) { const double v = block_sum_128(d[q], red); if (threadIdx.x == 0) out_d[(size_t)blockIdx.x * GS_D + q] = v; }
+    for (int q = 0; q < GS_I; ++q) { const double v = block_sum_128(c[q], red); if (threadIdx.x == 0) out_i[(size_t)blockIdx.x * GS_I + q] = (long long)v; }
+}
+
+// what the all-gather carries per chain: final energy, mean energy, acceptance, production mean
+__global__ void k_chain_finals(const ChainCtl *ctl, int n_local, int width, double *out)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= width) return;
+    double v[4] = {0.0, 0.0, 0.0, 0.0};
+    if (c < n_local) {
+        const ChainCtl &s = ctl[c];
+        v[0] = s.toteng;
+        v[1] = s.nstat > 0 ? s.sum_e / (double)s.nstat : 0.0;
+        v[2] = s.step > 0 ? (double)s.nsuc / (double)s.step : 0.0;
+        v[3] = s.prod_acc > 0 ? s.production / (double)s.prod_acc : 0.0;   // PRODUCTION / PROD_ACC, MonteCarlo.F90:555-560
+    }
+    for (int q = 0; q < 4; ++q) out[(size_t)c * 4 + q] = v[q];
+}
+
+void block_of(int rank, int world, long long n_total, long long &start, long long &count)
+{
+    const long long base = n_total / world, rem = n_total % world;
+    count = base + (rank < rem ? 1 : 0);
+    start = (long long)rank * base + std::min<long long>(rank, rem);
+}
+
+}  // namespace
+
+struct mcb_comm_state {
+    ncclComm_t comm = nullptr;
+    bool owned = false;
+    int nranks = 1, rank = 0;
+    long long n_total = 0, offset = 0;
+    double *d_d = nullptr; long long *d_i = nullptr; size_t cap_groups = 0;
+    double *d_send = nullptr, *d_recv = nullptr; size_t cap_width = 0;
+};
+
+static int nccl_err(mcb_t *h, const char *what, ncclResult_t r)
+{
+    h->err = std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "NCCL error");
+    return -1000 - (int)r;
+}
+
+static void comm_free(mcb_t *h)
+{
+    mcb_comm_state *cs = h->comm;
+    if (!cs) return;
+    if (cs->comm && cs->owned && g_nccl.CommDestroy) g_nccl.CommDestroy(cs->comm);
+    cudaFree(cs->d_d); cudaFree(cs->d_i); cudaFree(cs->d_send); cudaFree(cs->d_recv);
+    delete cs;
+    h->comm = nullptr;
+}
+
+extern "C" int mcb_comm_get_unique_id(char id[MCB_COMM_ID_BYTES])
+{
+    static_assert(sizeof(ncclUniqueId) == MCB_COMM_ID_BYTES, "ncclUniqueId is 128 bytes");
+    if (!id) return 1;
+    if (nccl_bind()) return -1000;
+    ncclUniqueId u;
+    const ncclResult_t r = g_nccl.GetUniqueId(&u);
+    if (r != ncclSuccess) return -1000 - (int)r;
+    memcpy(id, &u, sizeof(u));
+    return 0;
+}
+
+static int comm_setup(mcb_t *h, ncclComm_t comm, bool owned, int nranks, int rank, int64_t n_total_chains)
+{
+    long long start = 0, count = 0;
+    block_of(rank, nranks, n_total_chains, start, count);
+    if (count != h->n_chains) {
+        if (owned && comm) g_nccl.CommDestroy(comm);
+        return arg_err(h, "mcb_comm_init: this handle's n_chains is not rank's block of n_total_chains (contiguous blocks, the first n_total % nranks ranks hold one chain more)");
+    }
+    comm_free(h);
+    mcb_comm_state *cs = new mcb_comm_state;
+    cs->comm = comm; cs->owned = owned; cs->nranks = nranks; cs->rank = rank; cs->n_total = n_total_chains; cs->offset = start;
+    h->comm = cs;
+    return 0;
+}
+
+extern "C" int mcb_comm_init(mcb_t *h, int nranks, int rank, const char id[MCB_COMM_ID_BYTES], int64_t n_total_chains)
+{
+    if (!h) return 1;
+    if (!id || nranks < 1 || rank < 0 || rank >= nranks || n_total_chains < nranks) return arg_err(h, "mcb_comm_init: bad argument");
+    if (const char *why = nccl_bind()) { h->err = why; return -1000; }
+    CK(h, cudaSetDevice(h->device));
+    ncclUniqueId u;
+    memcpy(&u, id, sizeof(u));
+    ncclComm_t comm = nullptr;
+    const ncclResult_t r = g_nccl.CommInitRank(&comm, nranks, u, rank);
+    if (r != ncclSuccess) return nccl_err(h, "ncclCommInitRank", r);
+    return comm_setup(h, comm, true, nranks, rank, n_total_chains);
+}
+
+extern "C" int mcb_comm_attach(mcb_t *h, void *nccl_comm, int nranks, int rank, int64_t n_total_chains)
+{
+    if (!h) return 1;
+    if (!nccl_comm || nranks < 1 || rank < 0 || rank >= nranks || n_total_chains < nranks) return arg_err(h, "mcb_comm_attach: bad argument");
+    if (const char *why = nccl_bind()) { h->err = why; return -1000; }
+    return comm_setup(h, static_cast<ncclComm_t>(nccl_comm), false, nranks, rank, n_total_chains);
+}
+
+extern "C" int mcb_comm_destroy(mcb_t *h)
+{
+    if (!h) return 1;
+    comm_free(h);
+    return 0;
+}
+
+extern "C" int mcb_reduce_stats(mcb_t *h, int64_t chains_per_group, mcb_global_stats *out, int n_groups)
+{
+    if (!h) return 1;
+    if (!out || n_groups < 1) return arg_err(h, "mcb_reduce_stats: null output or n_groups < 1");
+    mcb_comm_state local;          // without a communicator: this handle's chains alone (one rank)
+    mcb_comm_state *cs = h->comm;
+    if (!cs) { local.n_total = h->n_chains; cs = &local; }
+    const long long per = chains_per_group > 0 ? chains_per_group : cs->n_total;
+    if ((cs->n_total + per - 1) / per != n_groups) return arg_err(h, "mcb_reduce_stats: n_groups must be ceil(n_total_chains / chains_per_group)");
+    CK(h, cudaSetDevice(h->device));
+    if (int rc = ensure_prepared(h)) return rc;
+    double *d_d = cs->d_d; long long *d_i = cs->d_i;
+    if ((size_t)n_groups > cs->cap_groups) {
+        cudaFree(cs->d_d); cudaFree(cs->d_i); cs->d_d = nullptr; cs->d_i = nullptr; cs->cap_groups = 0;
+        CK(h, cudaMalloc(&cs->d_d, sizeof(double) * GS_D * n_groups));
+        CK(h, cudaMalloc(&cs->d_i, sizeof(long long) * GS_I * n_groups));
+        cs->cap_groups = n_groups;
+        d_d = cs->d_d; d_i = cs->d_i;
+    }
+    k_stats_groups<<<n_groups, BIG_TILE, 0, h->stream>>>(h->ctl, h->n_chains, cs->offset, per, d_d, d_i);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    if (cs->comm && cs->nranks > 1) {
+        ncclResult_t r = g_nccl.GroupStart();
+        if (r == ncclSuccess) r = g_nccl.AllReduce(d_d, d_d, (size_t)GS_D * n_groups, ncclDouble, ncclSum, cs->comm, h->stream);
+        if (r == ncclSuccess) r = g_nccl.AllReduce(d_i, d_i, (size_t)GS_I * n_groups, ncclInt64, ncclSum, cs->comm, h->stream);
+        const ncclResult_t r2 = g_nccl.GroupEnd();
+        if (r != ncclSuccess || r2 != ncclSuccess) return nccl_err(h, "ncclAllReduce", r != ncclSuccess ? r : r2);
+    }
+    std::vector<double> hd((size_t)GS_D * n_groups);
+    std::vector<long long> hi((size_t)GS_I * n_groups);
+    CK(h, cudaMemcpyAsync(hd.data(), d_d, sizeof(double) * hd.size(), cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaMemcpyAsync(hi.data(), d_i, sizeof(long long) * hi.size(), cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    if (cs == &local) { cudaFree(local.d_d); cudaFree(local.d_i); }
+    for (int g = 0; g < n_groups; ++g) {
+        mcb_global_stats &o = out[g];
+        o.sum_e = hd[GS_D * g]; o.sum_e2 = hd[GS_D * g + 1]; o.production = hd[GS_D * g + 2]; o.sum_toteng = hd[GS_D * g + 3];
+        o.n_stat = hi[GS_I * g]; o.prod_acc = hi[GS_I * g + 1]; o.nsuc = hi[GS_I * g + 2]; o.step = hi[GS_I * g + 3];
+        o.sitepairs = hi[GS_I * g + 4]; o.n_clamped = hi[GS_I * g + 5]; o.uniforms_used = hi[GS_I * g + 6]; o.n_chains = hi[GS_I * g + 7];
+    }
+    return 0;
+}
+
+extern "C" int mcb_gather_chains(mcb_t *h, double *out, int64_t n_total_chains)
+{
+    if (!h) return 1;
+    if (!out) return arg_err(h, "mcb_gather_chains: null output");
+    mcb_comm_state local;
+    mcb_comm_state *cs = h->comm;
+    if (!cs) { local.n_total = h->n_chains; cs = &local; }
+    if (n_total_chains != cs->n_total) return arg_err(h, "mcb_gather_chains: n_total_chains differs from the communicator's");
+    CK(h, cudaSetDevice(h->device));
+    if (int rc = ensure_prepared(h)) return rc;
+    const size_t width = (size_t)((cs->n_total + cs->nranks - 1) / cs->nranks);   // widest block; shorter ones are padded
+    if (width > cs->cap_width) {
+        cudaFree(cs->d_send); cudaFree(cs->d_recv); cs->d_send = cs->d_recv = nullptr; cs->cap_width = 0;
+        CK(h, cudaMalloc(&cs->d_send, sizeof(double) * 4 * width));
+        CK(h, cudaMalloc(&cs->d_recv, sizeof(double) * 4 * width * cs->nranks));
+        cs->cap_width = width;
+    }
+    k_chain_finals<<<(unsigned)((width + 127) / 128), 128, 0, h->stream>>>(h->ctl, h->n_chains, (int)width, cs->d_send);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    if (cs->comm && cs->nranks > 1) {
+        const ncclResult_t r = g_nccl.AllGather(cs->d_send, cs->d_recv, 4 * width, ncclDouble, cs->comm, h->stream);
+        if (r != ncclSuccess) return nccl_err(h, "ncclAllGather", r);
+    } else CK(h, cudaMemcpyAsync(cs->d_recv, cs->d_send, sizeof(double) * 4 * width, cudaMemcpyDeviceToDevice, h->stream));
+    std::vector<double> tmp(4 * width * cs->nranks);
+    CK(h, cudaMemcpyAsync(tmp.data(), cs->d_recv, sizeof(double) * tmp.size(), cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
+    for (int r = 0; r < cs->nranks; ++r) {
+        long long start = 0, count = 0;
+        block_of(r, cs->nranks, cs->n_total, start, count);
+        memcpy(out + 4 * start, tmp.data() + 4 * width * r, sizeof(double) * 4 * count);
+    }
+    if (cs == &local) { cudaFree(local.d_send); cudaFree(local.d_recv); }
     return 0;
 }

@@ -451,7 +451,7 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
         if (MAT_SMEM) for (int qq = lane; qq < N * MS; qq += 32) gimg[g.o_mat + qq] = img[g.o_mat + qq];
     }
     if (lane == 0) {
-        s.step += done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.uused += uused; s.prod_acc += prod_acc;
+        s.step += done; s.rng_n += (unsigned long long)done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.uused += uused; s.prod_acc += prod_acc;
         s.nstat += nstat; s.sitepairs += (long long)sitepairs;
         // REAL(NACCEPT)/REAL(NADJ) as METROPOLIS leaves it after its last step (:758): before the window reset
         if (done > 0) s.ratio = (double)((float)racc / (float)s.nadj);
@@ -564,9 +564,12 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
     unsigned nsuc = 0, nacc = (unsigned)s.naccept, racc = 0, nclamp = 0, n_used8 = 0, prod_acc = 0;
     unsigned long long sum_nn = 0;
     const unsigned long long step0 = (unsigned long long)s.step;
+    // position in the uniform stream: steps since mcb_seed_chains (NOT the statistics counter `step`, which
+    // mcb_reset_stats zeroes - the stream must go on where it was)
+    const unsigned long long pos0 = s.rng_n;
     const int nsteps_i = (int)min(nsteps, (long long)0x3fffffff);
     int ring_hi = 0;                                                // the ring holds the launch-local steps [ring_hi - 64, ring_hi)
-    const int ring0 = (int)(step0 & 63ULL);
+    const int ring0 = (int)(pos0 & 63ULL);
     // launch-local index of the first production step: step0 + k + 1 >= start_prod (MonteCarlo.F90:760)
     const long long pf = s.start_prod - (long long)step0 - 1;
     const int prod_from = pf <= 0 ? 0 : (pf > 0x3fffffff ? 0x7fffffff : (int)pf);
@@ -576,22 +579,24 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
 
     while (done < nsteps_i) {
         // ================= pre-draw the next 32 steps when the ring runs low (one step per lane) =================
-        while (done + T > ring_hi) {
-            const unsigned long long sidx = step0 + (unsigned)(ring_hi + lane);
-            const int e = (int)(sidx & 63ULL);
-            const double u0 = stream_uniform(s.rng_key, 8ULL * sidx);
-            int ii = (int)(u0 * (double)N) + 1;                     // MCINIT, MonteCarlo.F90:697-698
-            if (g.quirk31 && ii == 31) ii = 30;
-            ring_i[e] = min(ii, N) - 1;
+        while (done + T > ring_hi) {                                // (block-uniform condition; with W > 1 warp 0 fills for everybody)
+            if (W == 1 || warp == 0) {
+                const unsigned long long sidx = pos0 + (unsigned)(ring_hi + lane);
+                const int e = (int)(sidx & 63ULL);
+                const double u0 = stream_uniform(s.rng_key, 8ULL * sidx);
+                int ii = (int)(u0 * (double)N) + 1;                 // MCINIT, MonteCarlo.F90:697-698
+                if (g.quirk31 && ii == 31) ii = 30;
+                ring_i[e] = min(ii, N) - 1;
 #pragma unroll
-            for (int q = 0; q < 6; ++q) {                           // randVec / randVecHoek before the step size, lib.f90:111-131
-                const double rvu = (stream_uniform(s.rng_key, 8ULL * sidx + 1 + q) - 0.5) * 2.0;
-                ring_rv[6 * e + q] = (q < 3 ? INV_SQRT3 : 1.0) * rvu;
+                for (int q = 0; q < 6; ++q) {                       // randVec / randVecHoek before the step size, lib.f90:111-131
+                    const double rvu = (stream_uniform(s.rng_key, 8ULL * sidx + 1 + q) - 0.5) * 2.0;
+                    ring_rv[6 * e + q] = (q < 3 ? INV_SQRT3 : 1.0) * rvu;
+                }
+                // METROPOLIS draws RV <= E**x; with x < 0 that is log(RV)/log(E) <= x, and the left side needs only the uniform
+                ring_thr[e] = log(stream_uniform(s.rng_key, 8ULL * sidx + 7)) * (1.0 / LN_E_F32);
             }
-            // METROPOLIS draws RV <= E**x; with x < 0 that is log(RV)/log(E) <= x, and the left side needs only the uniform
-            ring_thr[e] = log(stream_uniform(s.rng_key, 8ULL * sidx + 7)) * (1.0 / LN_E_F32);
             ring_hi += 32;
-            __syncwarp();
+            if (W > 1) __syncthreads(); else __syncwarp();
         }
         // ================= evaluation of step (done + gidx) by this group =================
         const int ring_e = (ring0 + done + gidx) & 63;
@@ -702,7 +707,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
         for (int o = GL / 2; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
         // METROPOLIS (:720-788) on DELTA = dE
         const double exponent = dE * neg_inv_rt;
-        const bool clamped = !(fabs(dE) <= DBL_HUGE);                // Inf/NaN trial energy: clamped, rejected (:421-428)
+        const bool clamped = !(dE <= DBL_HUGE);                      // +Inf/NaN trial energy: clamped, rejected (:421-428); -Inf passes, as there
         const bool used8 = !clamped && exponent >= -75.0 && exponent < 0.0;
         const bool accept = !clamped && (exponent >= 0.0 || (used8 && thr <= exponent));
         if (T > 1 && r == 0) {
@@ -851,7 +856,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
         if (MAT_SMEM) for (int qq = tid; qq < N * MS; qq += 32 * W) gimg[g.o_mat + qq] = img[g.o_mat + qq];
     }
     if (tid == 0) {
-        s.step += done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.prod_acc += prod_acc;
+        s.step += done; s.rng_n += (unsigned long long)done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.prod_acc += prod_acc;
         s.uused += 7LL * done + n_used8;                                      // 7 uniforms per step, an 8th when METROPOLIS draws
         s.nstat += done > prod_from ? done - prod_from : 0;                   // steps at or after start_prod
         s.sitepairs += (long long)wpair * (long long)sum_nn + (long long)wsol * done;

@@ -95,7 +95,8 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
     unsigned long long sitepairs = 0;
     const unsigned long long step0 = (unsigned long long)s.step;
     const int nsteps_i = (int)min(nsteps, (long long)0x3fffffff);
-    unsigned long long gen_end = step0;
+    const unsigned long long pos0 = s.rng_n;   // position in the uniform stream (steps since mcb_seed_chains), see k_run_spec
+    unsigned long long gen_end = pos0;
     const long long pf = s.start_prod - (long long)step0 - 1;     // launch-local index of the first production step (:760)
     const int prod_from = pf <= 0 ? 0 : (pf > 0x3fffffff ? 0x7fffffff : (int)pf);
     // list of the NEXT step's molecule (known from the ring), fetched one step ahead: count, candidates, build position
@@ -125,7 +126,7 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
             nrebuild++;
             __syncwarp();
         }
-        while (step0 + (unsigned)done + 2 > gen_end) {   // pre-draw the next 32 steps, one step per lane (as k_run_spec)
+        while (pos0 + (unsigned)done + 2 > gen_end) {   // pre-draw the next 32 steps, one step per lane (as k_run_spec)
             const unsigned long long sidx = gen_end + (unsigned)lane;
             const int e = (int)(sidx & 63ULL);
             const double u0 = stream_uniform(s.rng_key, 8ULL * sidx);
@@ -141,7 +142,7 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
             gen_end += 32;
             __syncwarp();
         }
-        const int ring_e = (int)((step0 + (unsigned)done) & 63ULL);
+        const int ring_e = (int)((pos0 + (unsigned)done) & 63ULL);
         const int i = ring_i[ring_e];
         const double thr = ring_thr[ring_e];
         const double old_tot = rowsum[i] + energy[i];
@@ -162,7 +163,7 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
 #pragma unroll
         for (int q = 0; q < 2; ++q) cold[q] = cj[q] >= 0 ? mat[(size_t)i * MS + cj[q]] : 0.0;
         if (lists_on) {   // the next step's list (lists only change in a rebuild, which clears p_valid)
-            const int in = ring_i[(int)((step0 + (unsigned)done + 1ULL) & 63ULL)];
+            const int in = ring_i[(int)((pos0 + (unsigned)done + 1ULL) & 63ULL)];
             p_cnt = vcnt[in];
             p_idx[0] = (int)vidx[(size_t)in * VL_K + lane]; p_idx[1] = (int)vidx[(size_t)in * VL_K + 32 + lane];
             p_rfx = vref[in]; p_rfy = vref[Np + in]; p_rfz = vref[2 * Np + in];
@@ -239,7 +240,7 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
         for (int o = 16; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
         // ---- METROPOLIS (:720-788) on DELTA = dE
         const double exponent = dE * neg_inv_rt;
-        const bool clamped = !(fabs(dE) <= DBL_HUGE);
+        const bool clamped = !(dE <= DBL_HUGE);   // -Inf is not clamped (MonteCarlo.F90:421-428)
         const bool used8 = !clamped && exponent >= -75.0 && exponent < 0.0;
         const bool accept = !clamped && (exponent >= 0.0 || (used8 && thr <= exponent));
         if (accept) {
@@ -302,7 +303,7 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
         for (int qq = lane; qq < n_mut; qq += 32) gimg[qq] = img[qq];
     }
     if (lane == 0) {
-        s.step += done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.uused += uused; s.prod_acc += prod_acc;
+        s.step += done; s.rng_n += (unsigned long long)done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.uused += uused; s.prod_acc += prod_acc;
         s.nstat += nstat; s.sitepairs += (long long)sitepairs;
         if (done > 0) s.ratio = (double)((float)racc / (float)s.nadj);
         ctl[c] = s;

@@ -116,7 +116,8 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
     const unsigned long long step0 = (unsigned long long)s.step;
     const int nsteps_i = (int)min(nsteps, (long long)0x3fffffff);
     int ring_hi = 0;                                               // the ring holds the launch-local steps [ring_hi - 64, ring_hi)
-    const int ring0 = (int)(step0 & 63ULL);
+    const unsigned long long pos0 = s.rng_n;   // position in the uniform stream (steps since mcb_seed_chains), see k_run_spec
+    const int ring0 = (int)(pos0 & 63ULL);
     const long long pf = s.start_prod - (long long)step0 - 1;     // launch-local index of the first production step (:760)
     const int prod_from = pf <= 0 ? 0 : (pf > 0x3fffffff ? 0x7fffffff : (int)pf);
     // list of a later step's molecule, fetched ahead: count, candidates, build position; p_step says for which step
@@ -147,7 +148,7 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
         }
         if (done + 2 * W > ring_hi) {                                   // pre-draw 32 steps, one per lane (as k_run_spec); warp 0 fills
             if (warp == 0) {
-                const unsigned long long sidx = step0 + (unsigned)(ring_hi + lane);
+                const unsigned long long sidx = pos0 + (unsigned)(ring_hi + lane);
                 const int e = (int)(sidx & 63ULL);
                 const double u0 = stream_uniform(s.rng_key, 8ULL * sidx);
                 int ii = (int)(u0 * (double)N) + 1;                 // MCINIT, MonteCarlo.F90:697-698
@@ -293,7 +294,7 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
             for (int o = 16; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
             // ---- METROPOLIS (:720-788) on DELTA = dE
             const double exponent = dE * neg_inv_rt;
-            clamped = !(fabs(dE) <= DBL_HUGE);
+            clamped = !(dE <= DBL_HUGE);   // -Inf is not clamped (MonteCarlo.F90:421-428)
             used8 = !clamped && exponent >= -75.0 && exponent < 0.0;
             accept = !clamped && (exponent >= 0.0 || (used8 && thr <= exponent));
         }
@@ -318,7 +319,6 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
             }
         const int nslots = nsolp + nn;
         // ---- commits, one after the other: two standing steps can share a neighbour whose row sum both adjust
-#pragma unroll
         bool committed = false;
 #pragma unroll
         for (int cw = 0; cw < W; ++cw) {
@@ -398,7 +398,7 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
         for (int qq = tid; qq < n_mut; qq += NT) gimg[qq] = img[qq];
     }
     if (tid == 0) {
-        s.step += done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.prod_acc += prod_acc;
+        s.step += done; s.rng_n += (unsigned long long)done; s.nsuc += nsuc; s.naccept = nacc; s.nclamp += nclamp; s.prod_acc += prod_acc;
         s.uused += 7LL * done + n_used8;
         s.nstat += done > prod_from ? done - prod_from : 0;
         s.sitepairs += (long long)wpair * (long long)sum_nn + (long long)wsol * done;

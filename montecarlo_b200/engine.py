@@ -189,6 +189,52 @@ class LJEngine:
         return {n: raw[n].copy() for n in raw.dtype.names}
 
 
+    # -- end of run: the job's one collective (NCCL inside libmcb200.so; PostProcess.F90:202-256 in the reference)
+    def comm_init(self, nranks: int, rank: int, unique_id: bytes, n_total_chains: int):
+        """Join the job's NCCL communicator; `unique_id` are the 128 bytes rank 0 got from comm_unique_id()."""
+        assert len(unique_id) == _lib.COMM_ID_BYTES
+        self._ck(self.lib.mcb_comm_init(self.h, int(nranks), int(rank), unique_id, int(n_total_chains)), "mcb_comm_init")
+        self._n_total = int(n_total_chains)
+
+    def comm_destroy(self):
+        self._ck(self.lib.mcb_comm_destroy(self.h), "mcb_comm_destroy")
+        self._n_total = None
+
+    def reduce_stats(self, chains_per_group: int = 0) -> dict:
+        """Sums over all chains of all ranks, per group of `chains_per_group` consecutive global chains (0: one group).
+        Returns arrays of length n_groups plus the derived mean_e, var_e, acceptance."""
+        n_total = getattr(self, "_n_total", None) or self.n_chains
+        per = chains_per_group if chains_per_group > 0 else n_total
+        ng = -(-n_total // per)
+        arr = (_lib.McbGlobalStats * ng)()
+        self._ck(self.lib.mcb_reduce_stats(self.h, int(chains_per_group), arr, ng), "mcb_reduce_stats")
+        raw = np.frombuffer(arr, dtype=np.dtype([(n, "f8" if t is C.c_double else "i8") for n, t in _lib.McbGlobalStats._fields_]))
+        out = {n: raw[n].copy() for n in raw.dtype.names}
+        n = np.maximum(out["n_stat"], 1)
+        out["mean_e"] = out["sum_e"] / n
+        out["var_e"] = np.maximum(out["sum_e2"] / n - out["mean_e"] ** 2, 0.0)
+        out["acceptance"] = out["nsuc"] / np.maximum(out["step"], 1)
+        return out
+
+    def gather_chains(self) -> dict:
+        """Four numbers per chain of the whole job, in global chain order, on every rank."""
+        n_total = getattr(self, "_n_total", None) or self.n_chains
+        out = np.empty((n_total, 4))
+        self._ck(self.lib.mcb_gather_chains(self.h, _d(out), n_total), "mcb_gather_chains")
+        return {"toteng": out[:, 0].copy(), "mean_e": out[:, 1].copy(), "acceptance": out[:, 2].copy(),
+                "production_mean": out[:, 3].copy()}
+
+
+def comm_unique_id() -> bytes:
+    """The 128-byte NCCL id rank 0 creates and hands to the other ranks (by MPI, a file, torch.distributed ...)."""
+    lib = _lib.load()
+    buf = C.create_string_buffer(_lib.COMM_ID_BYTES)
+    rc = lib.mcb_comm_get_unique_id(buf)
+    if rc != 0:
+        raise McbError(f"mcb_comm_get_unique_id failed ({rc}): is libnccl.so.2 installed?")
+    return buf.raw
+
+
 def measure_fp64_peak(device: int = -1, ms: float = 200.0) -> float:
     """Measured fp64 FMA peak in TFLOP/s (independent DFMA chains on every SM)."""
     lib = _lib.load()

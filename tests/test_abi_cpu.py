@@ -32,6 +32,8 @@ def test_struct_layouts_match_header():
     assert C.sizeof(McbParams) == 8 * 4 + 3 * 8 + 2 * 8
     assert C.sizeof(McbMcParams) == 6 * 8 + 2 * 4 + 8
     assert C.sizeof(McbChainStats) == 16 * 8
+    from montecarlo_b200._lib import McbGlobalStats, COMM_ID_BYTES
+    assert C.sizeof(McbGlobalStats) == 12 * 8 and COMM_ID_BYTES == 128
 
 
 def test_no_gpu_means_error_not_fallback(lib, shipped):

@@ -90,3 +90,19 @@ def test_check_box_follows_checknprep(shipped):
     far = box.com.copy(); far[0, 0] = 3.0 * box.boxl
     r = boxio.check_box(boxio.Box(**{**box.__dict__, "com": far, "energy": boxio.ENERGY_ABSENT}))
     assert r["info"][0] == "No energy detected in input box." and "outside" in r["info"][1]
+
+
+def test_dihedral_lines_are_fixed_columns(tmp_path, shipped):
+    """The reference reads dihedral lines with (I3,1X,I3,1X,F10.6) (MonteCarlo.F90:1123-1124): touching fields still
+    parse, and a rotation of 0 becomes -1 ("use the global one") in the text reader as in the unformatted one."""
+    assert boxio._dihedral_line("  8   1  90.000000") == (8, 1, 90.0)
+    assert boxio._dihedral_line("100 -12 -12.500000") == (100, -12, -12.5)
+    assert boxio._dihedral_line(" 12  13x-90.00000") == (12, 13, -90.0)      # column 8 is the 1X: whatever stands there is skipped
+    assert boxio._dihedral_line("  8   1   0.000000") == (8, 1, -1.0)
+    assert boxio._dihedral_line("  8   1") == (8, 1, -1.0)                  # short line: the field reads as blank = 0
+    assert boxio._dihedral_line("  8   1        30") == (8, 1, 30e-6)       # no decimal point: F10.6 implies six decimals
+    box, _ = shipped
+    b0 = boxio.Box(**{**box.__dict__, "dihedrals": [(8, 1, 0.0)]})
+    p, q = tmp_path / "z.txt", tmp_path / "z.bin"
+    boxio.write_box(b0, p); boxio.write_box_bin(b0, q)
+    assert boxio.read_box(p).dihedrals == boxio.read_box_bin(q).dihedrals == [(8, 1, -1.0)]

@@ -188,7 +188,8 @@ def test_single_step_mode_replays_reference_trace(shipped):
     box, system = shipped
     t = load_trace("ref_trace_10k.npz")
     rows, moved, acc = t["out_rows"], t["moved"], t["accepted"]
-    nstep = 3000
+    nstep = len(acc)          # all 10^4 steps of the fixture (BASELINE.json: >= 10^4)
+    assert nstep >= 10000
     eng = _engine(system, box.n, n_chains=1)
     eng.set_state(box.com, box.hoek)
     e0 = eng.total_energy()[0][0]
@@ -608,3 +609,254 @@ def test_fp64_peak_microbenchmark_is_sane():
     from montecarlo_b200.engine import measure_fp64_peak
     tf = measure_fp64_peak(0, 50.0)
     assert 10.0 < tf < 60.0, tf
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Kernel paths that are shipped but were not covered before: k_run_vl (one warp per chain with lists), k_run_steps with
+# the pair matrix in global memory, every COUL = true instantiation of the stepping kernels, single-step mode on a
+# global-matrix box, and the stream position across mcb_reset_stats.
+
+def _coulomb_system(system, box=None):
+    """conv = the physically meant factor (LennardJones.f90:52-56 before the `* 10**(-8)`), solute charges from the
+    reference's CHELPG stub run: the Coulomb sum then really moves energies and decisions."""
+    charges = json.loads((GOLD / "ref_charges.json").read_text())["charges"]
+    tab = system.sol_tab.copy(); tab[:, 0] = charges
+    kw = {"sol_tab": tab, "conv": ol.lib().mco_const_conv_intended()}
+    if box is not None:
+        kw.update(boxl=box.boxl, solute=box.solute)
+    return boxio.System(**{**system.__dict__, **kw})
+
+
+@pytest.mark.parametrize("case", ["vl_default_skin", "vl_small_skin"])
+def test_one_warp_list_kernel(shipped, case, monkeypatch):
+    """MCB200_NO_VL2=1: the N = 240 box steps with k_run_vl (one warp per chain, neighbour lists), the kernel that is
+    taken whenever k_run_vl2 does not fit.  Two launches, then new coordinates from the host and a third launch."""
+    box, system = shipped
+    b = boxio.replicate(box, 2)
+    s = _sys_for(system, b)
+    monkeypatch.setenv("MCB200_NO_VL2", "1")
+    if case == "vl_small_skin":
+        monkeypatch.setenv("MCB200_SKIN", "0.25")
+    nch, nsteps = 2, 4000
+    eng = _engine(s, b.n, n_chains=nch)
+    eng.set_state(b.com, b.hoek)
+    eng.seed(np.array([21, 22], dtype=np.uint64))
+    eng.run_steps(nsteps // 2)
+    eng.run_steps(nsteps // 2)
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    for c in range(nch):
+        o = ol.OracleChain(s, b.com, b.hoek)
+        o.total_energy()
+        o.run_steps_rng(nsteps, ol.rng_seed(21 + c), trace=False)
+        _compare_chain(st, c, o.stats(), com, hoek, o)
+    fresh = eng.total_energy()[0]
+    assert np.all(np.abs(fresh - st["toteng"]) <= RTOL * np.abs(fresh))
+    # lists must be rebuilt after coordinates arrive from the host (two distant molecules swapped)
+    d = np.linalg.norm(com[0] - com[0][0], axis=1)
+    far = int(np.argmax(d))
+    com2, hoek2 = com.copy(), hoek.copy()
+    com2[:, [0, far]] = com2[:, [far, 0]]
+    eng.set_state(com2, hoek2)
+    eng.reset_stats()
+    eng.set_mc_params()
+    eng.seed(np.array([41, 42], dtype=np.uint64))
+    eng.run_steps(1500)
+    st = eng.stats()
+    com3, hoek3 = eng.get_state()
+    for c in range(nch):
+        o = ol.OracleChain(s, com2[c], hoek2[c])
+        o.total_energy()
+        o.run_steps_rng(1500, ol.rng_seed(41 + c), trace=False)
+        _compare_chain(st, c, o.stats(), com3, hoek3, o)
+
+
+def test_one_warp_list_kernel_large_solute(shipped, monkeypatch):
+    """k_run_vl with more solute slots than one pass over the partner slots holds (37 solute atoms, N = 240)."""
+    monkeypatch.setenv("MCB200_NO_VL2", "1")
+    test_large_solute(shipped, 2)
+
+
+@pytest.mark.parametrize("which", ["replica", "forced_global"])
+def test_driver_uniforms_with_global_matrix(shipped, which):
+    """k_run_steps<*, MAT_SMEM = false>: the driver's own uniforms on a box whose pair matrix lives in global memory -
+    the 2x2x2 replica, and the shipped box with matrix_mode = 1."""
+    box, system = shipped
+    b = boxio.replicate(box, 2) if which == "replica" else box
+    s = _sys_for(system, b)
+    nch, nsteps = 3, 3000
+    u = np.random.default_rng(77).random((nch, 8 * nsteps))
+    eng = _engine(s, b.n, n_chains=nch, matrix_mode=1)
+    eng.set_state(b.com, b.hoek)
+    eng.set_mc_params(start_prod=1000, nadj=64)
+    consumed, steps = eng.run_steps(nsteps, u)
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    assert np.all(steps == nsteps)
+    for c in range(nch):
+        o = ol.OracleChain(s, b.com, b.hoek)
+        o.set_mc_params(start_prod=1000, nadj=64)
+        o.total_energy()
+        done, used, _ = o.run_steps(nsteps, u[c], trace=False)
+        assert done == nsteps and used == consumed[c] == st["uniforms_used"][c]
+        _compare_chain(st, c, o.stats(), com, hoek, o)
+    fresh = eng.total_energy()[0]
+    assert np.all(np.abs(fresh - st["toteng"]) <= RTOL * np.abs(fresh))
+
+
+@pytest.mark.parametrize("path", ["spec_n30", "spec_n30_lookahead4", "ubuf_n30", "ubuf_n240", "vl2_n240", "vl_n240", "spec_n240"])
+def test_coulomb_stepping_kernels(shipped, path, monkeypatch):
+    """conv != 0 through every stepping kernel (the reference's CONV is 0, LennardJones.f90:57, but the sum q1 q2 / r
+    must be carried, :52-56, :80-82): k_run_spec<true>, k_run_steps<true, *>, k_run_vl2<true>, k_run_vl<true>."""
+    box, system = shipped
+    big = path.endswith("n240")
+    b = boxio.replicate(box, 2) if big else box
+    s = _coulomb_system(system, b if big else None)
+    if path == "vl_n240":
+        monkeypatch.setenv("MCB200_NO_VL2", "1")
+    if path == "spec_n240":
+        monkeypatch.setenv("MCB200_NO_VERLET", "1")
+    nch, nsteps = 3, 2500 if big else 6000
+    eng = _engine(s, b.n, n_chains=nch, lookahead=4 if path.endswith("lookahead4") else 0)
+    eng.set_state(b.com, b.hoek)
+    tot0 = eng.total_energy()[0]
+    o0 = ol.OracleChain(s, b.com, b.hoek)
+    e0 = o0.total_energy()
+    lj_only = ol.OracleChain(_sys_for(system, b) if big else system, b.com, b.hoek).total_energy()
+    assert abs(e0 - lj_only) > 1.0 and np.all(np.abs(tot0 - e0) <= RTOL * abs(e0))
+    seeds = np.array([61, 62, 63], dtype=np.uint64)
+    if path.startswith("ubuf"):
+        u = np.random.default_rng(99).random((nch, 8 * nsteps))
+        consumed, steps = eng.run_steps(nsteps, u)
+        assert np.all(steps == nsteps)
+    else:
+        eng.seed(seeds)
+        eng.run_steps(nsteps // 2)
+        eng.run_steps(nsteps - nsteps // 2)
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    for c in range(nch):
+        o = ol.OracleChain(s, b.com, b.hoek)
+        o.total_energy()
+        if path.startswith("ubuf"):
+            done, used, _ = o.run_steps(nsteps, u[c], trace=False)
+            assert used == consumed[c]
+        else:
+            o.run_steps_rng(nsteps, ol.rng_seed(int(seeds[c])), trace=False)
+        _compare_chain(st, c, o.stats(), com, hoek, o)
+    fresh = eng.total_energy()[0]
+    assert np.all(np.abs(fresh - st["toteng"]) <= RTOL * np.abs(fresh))
+
+
+@pytest.mark.parametrize("coulomb", [False, True])
+def test_single_step_mode_on_global_matrix_box(shipped, coulomb):
+    """mcb_trial_delta / mcb_commit on the N = 240 replica (k_trial / k_commit with the matrix in global memory; with
+    conv != 0 also k_trial<true>): 1200 trial moves drawn the way MCINIT draws them, the oracle deciding."""
+    box, system = shipped
+    b = boxio.replicate(box, 2)
+    s = _coulomb_system(system, b) if coulomb else _sys_for(system, b)
+    eng = _engine(s, b.n, n_chains=2)
+    eng.set_state(b.com, b.hoek)
+    e0 = eng.total_energy()[0]
+    o = ol.OracleChain(s, b.com, b.hoek)
+    assert abs(o.total_energy() - e0[0]) <= RTOL * abs(e0[0])
+    rng = np.random.default_rng(123)
+    nacc = 0
+    for k in range(1200):
+        u = rng.random(8)
+        used, tr = o.step(u)                      # MCINIT + calculateLJ + METROPOLIS in the oracle
+        i = int(tr[4]); accepted = tr[5] != 0.0
+        ocom, ohoek = o.get_state()
+        if accepted:
+            nc, nh = ocom[i], ohoek[i]
+        else:                                     # rejected: replay MCINIT on a copy to get the trial position
+            o2 = ol.OracleChain(s, ocom, ohoek)
+            o2.set_mc_params(dposmax=tr[7], dhoekmax=tr[8])
+            j = o2.L.mco_mcinit(o2.h, ol._ptr(np.ascontiguousarray(u[:7])))
+            assert j == i
+            c2, h2 = o2.get_state()
+            nc, nh = c2[i], h2[i]
+        # chain 0 follows the oracle's decisions; chain 1 rejects everything and must stay where it started
+        d_e, e_new = eng.trial_delta([i + 1, i + 1], np.stack([nc, nc]), np.stack([nh, nh]))
+        scale = max(abs(tr[0]), abs(tr[1]))
+        assert abs(e_new[0] - tr[0]) <= RTOL * scale, (k, e_new[0], tr[0])
+        assert abs(d_e[0] - (tr[0] - tr[1])) <= RTOL * scale, (k, d_e[0], tr[0] - tr[1])
+        eng.commit([1 if accepted else 0, 0])
+        nacc += accepted
+    assert nacc > 100
+    st = eng.stats()
+    so = o.stats()
+    assert abs(st["toteng"][0] - so["toteng"]) <= RTOL * abs(so["toteng"]) and st["toteng"][1] == e0[1]
+    com, hoek = eng.get_state()
+    ocom, ohoek = o.get_state()
+    assert np.abs(com[0] - ocom).max() == 0.0 and np.abs(hoek[0] - ohoek).max() == 0.0
+    assert np.array_equal(com[1], b.com) and np.array_equal(hoek[1], b.hoek)
+    fresh = eng.total_energy()[0]
+    assert abs(fresh[0] - so["toteng"]) <= RTOL * abs(fresh[0]) and abs(fresh[1] - e0[1]) <= RTOL * abs(e0[1])
+
+
+@pytest.mark.parametrize("k", [1, 2])
+def test_reset_stats_keeps_the_stream_position(shipped, k):
+    """mcb_reset_stats zeroes the counters but not the position in the built-in uniform stream: equilibrate, reset,
+    produce must continue the stream (an oracle that simply keeps going), not replay the equilibration's numbers."""
+    box, system = shipped
+    b = boxio.replicate(box, 2) if k == 2 else box
+    s = _sys_for(system, b) if k == 2 else system
+    n_eq, n_prod = 1500, 2500             # the reset falls on an adaptation boundary (nadj = 100), where NACCEPT is 0 anyway
+    seeds = np.array([91, 92], dtype=np.uint64)
+    eng = _engine(s, b.n, n_chains=2)
+    eng.set_state(b.com, b.hoek)
+    eng.seed(seeds)
+    eng.run_steps(n_eq)
+    eq = eng.stats()
+    eng.reset_stats()
+    assert np.all(eng.stats()["step"] == 0) and np.all(eng.stats()["dposmax"] == eq["dposmax"])
+    eng.run_steps(n_prod)
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    for c in range(2):
+        o = ol.OracleChain(s, b.com, b.hoek)
+        o.total_energy()
+        rng = ol.rng_seed(int(seeds[c]))
+        o.run_steps_rng(n_eq, rng, trace=False)
+        so_eq = o.stats()
+        o.run_steps_rng(n_prod, rng, trace=False)
+        so = o.stats()
+        assert st["step"][c] == n_prod and st["nsuc"][c] == so["nsuc"] - so_eq["nsuc"]
+        assert st["sitepairs"][c] == so["sitepairs"] - so_eq["sitepairs"]
+        assert abs(st["toteng"][c] - so["toteng"]) <= RTOL * abs(so["toteng"])
+        ocom, ohoek = o.get_state()
+        assert np.abs(com[c] - ocom).max() <= 1e-12 and np.abs(hoek[c] - ohoek).max() <= 1e-12
+    # a replay of the equilibration's numbers would have reproduced the first n_eq decisions: it must not
+    eng2 = _engine(s, b.n, n_chains=2)
+    eng2.set_state(b.com, b.hoek)
+    eng2.seed(seeds)
+    eng2.run_steps(n_eq)
+    c_eq, _ = eng2.get_state()
+    eng2.reset_stats()
+    eng2.run_steps(1)
+    # re-seeding is what rewinds the stream
+    eng2.seed(seeds)
+    eng2.set_state(b.com, b.hoek)
+    eng2.set_mc_params()
+    eng2.reset_stats()
+    eng2.run_steps(n_eq)
+    c_again, _ = eng2.get_state()
+    assert np.array_equal(c_eq, c_again)
+
+
+def test_row_energy_refuses_while_a_trial_is_pending(shipped):
+    box, system = shipped
+    from montecarlo_b200.engine import McbError
+    eng = _engine(system, box.n, n_chains=1)
+    eng.set_state(box.com, box.hoek)
+    eng.total_energy()
+    eng.trial_delta([3], box.com[2] + 0.1, box.hoek[2])
+    with pytest.raises(McbError, match="pending"):
+        eng.row_energy(0, 3)
+    eng.commit([1])
+    row, ei = eng.row_energy(0, 3)
+    com, hoek = eng.get_state()
+    o = ol.OracleChain(system, com[0], hoek[0])
+    _, orow, oei = o.row_energy(2)
+    assert _close(row, orow, scale=np.abs(orow) + 1e-3) and _close(ei, oei)

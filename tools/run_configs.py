@@ -24,7 +24,7 @@ import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
 from montecarlo_b200 import boxio, dihedral, partition, postprocess  # noqa: E402
-from montecarlo_b200.engine import LJEngine  # noqa: E402
+from montecarlo_b200.engine import LJEngine, comm_unique_id  # noqa: E402
 
 
 def main():
@@ -77,12 +77,21 @@ def main():
     ms = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    st = eng.stats()
+    # the job's one collective, through the C ABI (NCCL inside libmcb200.so); torch.distributed only carries the id
+    if world > 1:
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        eng.comm_init(world, rank, idt.cpu().numpy().tobytes(), n_total)
     c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    c0.record()
-    tot = partition.reduce_stats(st, device="cuda")                               # the one all-reduce
-    mean_e = partition.gather_per_chain(st["sum_e"] / np.maximum(st["n_stat"], 1), n_total, device="cuda")   # the one all-gather
-    c1.record(); torch.cuda.synchronize()
+    torch.cuda.synchronize()
+    c0.record(stream)
+    g = eng.reduce_stats()                                                        # the one all-reduce
+    per_group = eng.reduce_stats(per_angle) if args.config == 4 else None         # (config 4: per dihedral angle)
+    mean_e = eng.gather_chains()["mean_e"]                                        # the one all-gather
+    c1.record(stream); torch.cuda.synchronize()
+    tot = {k: float(v[0]) for k, v in g.items()}
     if rank == 0:
         sec = ms.item() * 1e-3
         line = {"config": args.config, "n_gpus": world, "n_molecules": b.n, "chains": n_total, "steps_per_chain": args.steps,
@@ -93,6 +102,8 @@ def main():
             per = mean_e[: per_angle * len(angles)].reshape(len(angles), per_angle)
             e_angle = per.mean(axis=1)
             line["per_angle_mean_energy"] = [round(float(v), 4) for v in e_angle]
+            # the grouped all-reduce gives the same per-angle means from sums (weights: production samples per chain)
+            line["per_angle_mean_energy_allreduce"] = [round(float(v), 4) for v in per_group["mean_e"][: len(angles)]]
             line["per_angle_sem"] = [round(float(v), 4) for v in per.std(axis=1) / np.sqrt(per_angle)]
             # window hopping over the gathered energies: one "run" per chain index inside an angle block
             rng = np.random.default_rng(2026)
