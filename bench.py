@@ -310,9 +310,10 @@ def run_gpu_arm(args):
     b.record(stream)
     torch.cuda.synchronize()
     stats_ms = a.elapsed_time(b)
+    st_end = eng.stats()
     assert finals["toteng"].shape[0] == nch * world and int(gstats["n_chains"][0]) == nch * world
-    assert int(gstats["step"][0]) == int(m1["st1"]["step"].sum()) * world
-    assert np.array_equal(finals["toteng"][rank * nch:(rank + 1) * nch], m1["st1"]["toteng"])
+    assert int(gstats["step"][0]) == int(st_end["step"].sum()) * world      # every rank made the same number of steps
+    assert np.array_equal(finals["toteng"][rank * nch:(rank + 1) * nch], st_end["toteng"])
     eng.close()
 
     # ---- leg 2 = the box north_star's target is quoted on: 2x2x2 replica, configs[2]'s per-GPU share of chains
