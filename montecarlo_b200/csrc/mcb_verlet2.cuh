@@ -30,7 +30,7 @@ __host__ __device__ inline int vl2_list_doubles(int slots) { return (((slots + 1
 __host__ __device__ inline int vl2_smem_doubles(const Geo &g, int w)
 {
     const int small = vl2_small_slots(g);
-    return g.stage_doubles + w * (vl2_list_doubles(small) + 4 * small) + 64 + 6 * 64 + 32 + g.Np + 2 * VL2_MAX_W;
+    return g.stage_doubles + w * (vl2_list_doubles(small) + 4 * small) + 64 + 6 * 64 + 32 + 2 * VL2_MAX_W;
 }
 
 template <bool COUL, int W>
@@ -68,7 +68,6 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
     double *const ring_thr = p; p += 64;
     double *const ring_rv = p; p += 6 * 64;
     int *const ring_i = reinterpret_cast<int *>(p); p += 32;
-    double *const rowsum = p; p += Np;
     Vl2X *const xch = reinterpret_cast<Vl2X *>(p);
     unsigned short *const vidx = vb.idx + (size_t)c * N * VL_K;
     int *const vcnt = vb.cnt + (size_t)c * (N + 2);
@@ -78,21 +77,32 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
     for (int q = lane; q < small; q += 32) list[q] = q < nsolp ? N + q : 0;   // solute slots first; the rest valid indices
     if (warp == 0) for (int q = lane; q < nsolp; q += 32) list_g[q] = N + q;
     __syncthreads();
-    for (int j = tid; j < N; j += NT) {   // row sums from the stored matrix (symmetric: column sums, coalesced)
-        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-        int i = 0;
-        for (; i + 3 < N; i += 4) {
-            a0 += mat[(size_t)i * MS + j]; a1 += mat[(size_t)(i + 1) * MS + j];
-            a2 += mat[(size_t)(i + 2) * MS + j]; a3 += mat[(size_t)(i + 3) * MS + j];
-        }
-        for (; i < N; ++i) a0 += mat[(size_t)i * MS + j];
-        rowsum[j] = (a0 + a1) + (a2 + a3);
-    }
-    __syncthreads();
-    {
+    // TOTENG carries over from the previous launch (ChainCtl).  The O(N^2) pass over the stored matrix that re-anchors
+    // it - so that rounding of the running sum cannot pile up for ever - only runs when this launch crosses a multiple of
+    // 2^20 steps of the chain's stream: at 4000 steps per launch it used to be a quarter of the launch time.
+    if (((s.rng_n + (unsigned long long)max(nsteps, 0LL)) >> 20) != (s.rng_n >> 20)) {
+        double *const colsum = epart;   // (this warp's work area is free until the first step)
         double acc = 0.0;
-        for (int i = lane; i < N; i += 32) acc += fma(0.5, rowsum[i], energy[i]);
-        s.toteng = warp_sum(acc);
+        for (int j0 = 0; j0 < N; j0 += NT) {
+            const int j = j0 + tid;
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+            if (j < N) {
+                int i = 0;
+                for (; i + 3 < N; i += 4) {
+                    a0 += mat[(size_t)i * MS + j]; a1 += mat[(size_t)(i + 1) * MS + j];
+                    a2 += mat[(size_t)(i + 2) * MS + j]; a3 += mat[(size_t)(i + 3) * MS + j];
+                }
+                for (; i < N; ++i) a0 += mat[(size_t)i * MS + j];
+                acc += fma(0.5, (a0 + a1) + (a2 + a3), energy[j]);
+            }
+        }
+        acc = warp_sum(acc);
+        if (lane == 0) colsum[0] = acc;
+        __syncthreads();
+        double tot = 0.0;
+        for (int w = 0; w < W; ++w) tot += (smem + g.stage_doubles + w * (vl2_list_doubles(small) + 4 * small) + vl2_list_doubles(small))[0];
+        s.toteng = tot;
+        __syncthreads();
     }
     // lists are usable only if the reference's minimum image is a true metric: all centres of mass inside the box
     bool inside = true;
@@ -124,7 +134,30 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
     int p_cnt = -1, p_idx[2] = {0, 0}, p_step = -1;
     double p_rfx = 0.0, p_rfy = 0.0, p_rfz = 0.0;
 
+    Vl2X pend[W];
+    int pend_n = 0, pend_done = 0;
+    auto sum_stats = [&]() {   // TOTENG, production and energy sums of the steps committed by the previous batch, in step order
+#pragma unroll
+        for (int gg = 0; gg < W; ++gg) {
+            if (gg < pend_n) {
+                const Vl2X x = pend[gg];
+                const bool acc = (x.flags & 1) != 0;
+                n_used8 += (x.flags >> 1) & 1;
+                nclamp += (x.flags >> 2) & 1;
+                sum_nn += (unsigned)x.nn;
+                s.last_delta = x.dE;
+                const bool in_prod = pend_done + gg >= prod_from;    // selects instead of branches: adding 0.0 changes nothing
+                nsuc += acc;
+                s.toteng += acc ? x.dE : 0.0;
+                s.production += acc && in_prod ? s.toteng : 0.0; prod_acc += acc && in_prod;
+                const double te = in_prod ? s.toteng : 0.0;
+                s.sum_e += te; s.sum_e2 = fma(te, te, s.sum_e2);
+            }
+        }
+        pend_n = 0;
+    };
     while (done < nsteps_i) {
+        if (warp == 0) sum_stats();
         if (need_rebuild) {
             // ---- (re)build every list from the current centres of mass, which become the reference positions
             for (int j = tid; j < 3 * Np; j += NT) vref[j] = com[j];
@@ -171,8 +204,7 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
         const int ring_e = (ring0 + k) & 63;
         const int i = ring_i[ring_e];
         const double thr = ring_thr[ring_e];
-        const double old_tot = rowsum[i] + energy[i];
-        const double old_part = lane == 0 ? old_tot : 0.0;
+        const double e_old = energy[i];
         // ---- candidates of molecule i (fetched during an earlier batch if the guess of this step's index was right)
         if (lists_on && p_step != k) {
             p_cnt = vcnt[i];
@@ -233,7 +265,7 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
         bool cin[2] = {false, false};
         int cslot[2] = {0, 0};
         double dE = 0.0, esol = 0.0;
-        double cval[2] = {0.0, 0.0}, cdel[2] = {0.0, 0.0};
+        double cval[2] = {0.0, 0.0};
         bool cchg[2] = {false, false};
         bool clamped = false, used8 = false, accept = false;
         if (evaluate) {
@@ -271,6 +303,12 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
                 for (int sb = 0; sb < nslots; sb += 2 * 8)
                     lane_tot += items_staged<COUL, 2>(g, sites, tabAB, tabQ, list_g, nsolp, nslots, sb + sub, 8, a, sx, sy, sz, epart_g);
             }
+            // TOTENG_new - TOTENG_old = sum(new row) + ENERGY_new(i) - sum(old row) - ENERGY(i).  The old row's non-zero
+            // entries all belong to listed candidates (a partner inside the cutoff is inside cutoff + skin), so with a
+            // list the old row is summed from the entries fetched above; the full scan reads the whole row.
+            double old_part = lane == 0 ? e_old : 0.0;
+            if (use_list) old_part += cold[0] + cold[1];
+            else for (int j = lane; j < N; j += 32) old_part += mat[(size_t)i * MS + j];
             dE = lane_tot - old_part;
             __syncwarp();
             const double *const ep = use_list ? epart : epart_g;
@@ -281,7 +319,6 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
                     const int sl = cin[q] ? cslot[q] : 0;
                     const double2 e01 = *reinterpret_cast<const double2 *>(epart + 4 * sl), e23 = *reinterpret_cast<const double2 *>(epart + 4 * sl + 2);
                     cval[q] = cin[q] ? (e01.x + e01.y) + (e23.x + e23.y) : 0.0;
-                    cdel[q] = cval[q] - cold[q];
                     cchg[q] = cj[q] >= 0 && (cin[q] || cold[q] != 0.0);
                 }
             }
@@ -318,44 +355,36 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
                 acc_valid |= (unsigned)(xs[q].flags & 1) << q;
             }
         const int nslots = nsolp + nn;
-        // ---- commits, one after the other: two standing steps can share a neighbour whose row sum both adjust
-        bool committed = false;
+        // ---- commits, all at once: the standing accepted steps moved different molecules, none of which any other
+        //      standing step looked at, so they write different matrix entries and different molecules' coordinates;
+        //      nothing shared is read-modified-written (the old row is summed from the matrix entries, see above)
+        if (warp < progress && accept) {
+            if (use_list) {
 #pragma unroll
-        for (int cw = 0; cw < W; ++cw) {
-            if (cw >= progress || !(xs[cw].flags & 1)) continue;                    // uniform over the block
-            if (committed) __syncthreads();
-            committed = true;
-            if (warp == cw) {
-                if (use_list) {
-#pragma unroll
-                    for (int q = 0; q < 2; ++q)
-                        if (cchg[q]) {   // SS(i,j) = SS(j,i) = EN inside the cutoff (:819-820), 0 for a partner that left it
-                            const int j = cj[q];
-                            rowsum[j] += cdel[q];
-                            mat[(size_t)i * MS + j] = cval[q]; mat[(size_t)j * MS + i] = cval[q];
-                        }
-                } else {
-                    // full scan: partners that left the cutoff, then the partners inside it
-                    for (int j = lane; j < N; j += 32) {
-                        const double old = mat[(size_t)i * MS + j];
-                        if (old != 0.0 && j != i && pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2) {
-                            rowsum[j] -= old;
-                            mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0;
-                        }
+                for (int q = 0; q < 2; ++q)
+                    if (cchg[q]) {   // SS(i,j) = SS(j,i) = EN inside the cutoff (:819-820), 0 for a partner that left it
+                        const int j = cj[q];
+                        mat[(size_t)i * MS + j] = cval[q]; mat[(size_t)j * MS + i] = cval[q];
                     }
-                    for (int sl = nsolp + lane; sl < nslots; sl += 32) {
-                        const int j = list_g[sl];
-                        const double e = (epart_g[4 * sl] + epart_g[4 * sl + 1]) + (epart_g[4 * sl + 2] + epart_g[4 * sl + 3]);
-                        rowsum[j] += e - mat[(size_t)i * MS + j];
-                        mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
+            } else {
+                // full scan: partners that left the cutoff, then the partners inside it
+                for (int j = lane; j < N; j += 32) {
+                    const double old = mat[(size_t)i * MS + j];
+                    if (old != 0.0 && j != i && pair_r2(com[j] - ncx, com[Np + j] - ncy, com[2 * Np + j] - ncz, g) > g.cut2) {
+                        mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0;
                     }
                 }
-                if (lane >= 1 && lane <= 6) base[i] = nv;
-                if (lane < 4) {
-                    sites[SITE_DOUBLES * i + 3 * a] = sx; sites[SITE_DOUBLES * i + 3 * a + 1] = sy; sites[SITE_DOUBLES * i + 3 * a + 2] = sz;
+                for (int sl = nsolp + lane; sl < nslots; sl += 32) {
+                    const int j = list_g[sl];
+                    const double e = (epart_g[4 * sl] + epart_g[4 * sl + 1]) + (epart_g[4 * sl + 2] + epart_g[4 * sl + 3]);
+                    mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
                 }
-                if (lane == 0) { energy[i] = esol; rowsum[i] = (dE + old_tot) - esol; }
             }
+            if (lane >= 1 && lane <= 6) base[i] = nv;
+            if (lane < 4) {
+                sites[SITE_DOUBLES * i + 3 * a] = sx; sites[SITE_DOUBLES * i + 3 * a + 1] = sy; sites[SITE_DOUBLES * i + 3 * a + 2] = sz;
+            }
+            if (lane == 0) energy[i] = esol;
         }
         // ---- bookkeeping in step order: every warp tracks what steers the chain (accepted moves of the adaptation
         //      window, list validity); the energy statistics only live on warp 0, whose lane 0 writes them back
@@ -366,20 +395,13 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
                 const bool acc = (x.flags & 1) != 0;
                 nacc += acc;
                 if (lists_on && acc && (x.flags & 8)) need_rebuild = true;   // the molecule now sits more than skin/2 from its build position
-                if (warp == 0) {
-                    n_used8 += (x.flags >> 1) & 1;
-                    nclamp += (x.flags >> 2) & 1;
-                    sum_nn += (unsigned)x.nn;
-                    s.last_delta = x.dE;
-                    const bool in_prod = done + gg >= prod_from;    // selects instead of branches: adding 0.0 changes nothing
-                    nsuc += acc;
-                    s.toteng += acc ? x.dE : 0.0;
-                    s.production += acc && in_prod ? s.toteng : 0.0; prod_acc += acc && in_prod;
-                    const double te = in_prod ? s.toteng : 0.0;
-                    s.sum_e += te; s.sum_e2 = fma(te, te, s.sum_e2);
-                }
             }
         }
+        // the energy statistics of this batch (warp 0) are summed at the top of the next one, off the stretch where
+        // every other warp waits at the batch's last barrier
+#pragma unroll
+        for (int gg = 0; gg < W; ++gg) pend[gg] = xs[gg];
+        pend_n = progress; pend_done = done;
         racc = nacc;
         adj_count += progress;
         if (adj_count == s.nadj) {                                  // mod(I, NADJ) == 0, :766-777
@@ -393,6 +415,7 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
         done += progress;
         __syncthreads();
     }
+    if (warp == 0) sum_stats();
     {
         const int n_mut = g.o_sites + SITE_DOUBLES * N;
         for (int qq = tid; qq < n_mut; qq += NT) gimg[qq] = img[qq];

@@ -4,6 +4,7 @@
     MCB200_LIB=montecarlo_b200/libmcb200_prof.so python tools/phase_clocks.py
 """
 import ctypes as C
+import os
 import sys
 from pathlib import Path
 
