@@ -130,7 +130,8 @@ static void setup_geo(mcb_handle *h)
         }
     }
     h->smem_bytes = ((size_t)g.stage_doubles + g.work_doubles) * 8;
-    h->smem_spec_bytes = ((size_t)g.stage_doubles + (size_t)h->lookahead * (g.work_doubles + SPECX_DOUBLES) + 64 + 6 * 64 + 32 + g.Np + 2) * 8;
+    // image + look-ahead work areas + exchange + ring (threshold, moves, picks) + tot[] + sin/cos cache + ring of sin/cos + moved bits
+    h->smem_spec_bytes = ((size_t)g.stage_doubles + (size_t)h->lookahead * (g.work_doubles + SPECX_DOUBLES) + 64 + 6 * 64 + 32 + g.Np + 6 * g.Np + 6 * 64 + (g.N + 63) / 64 + 2) * 8;
     h->can_step = h->smem_spec_bytes <= 227 * 1024;
 }
 
@@ -281,7 +282,10 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
 #define SPEC_ATTR1(GL, W, S) rc |= set_smem_attr(h, k_run_spec<false, false, GL, W, S>, h->smem_spec_bytes); rc |= set_smem_attr(h, k_run_spec<false, true, GL, W, S>, h->smem_spec_bytes); \
                             rc |= set_smem_attr(h, k_run_spec<true, false, GL, W, S>, h->smem_spec_bytes);  rc |= set_smem_attr(h, k_run_spec<true, true, GL, W, S>, h->smem_spec_bytes);
 #define SPEC_ATTR(GL, W) SPEC_ATTR1(GL, W, true) SPEC_ATTR1(GL, W, false)
-        SPEC_ATTR(32, 1) SPEC_ATTR(16, 1) SPEC_ATTR(8, 1) SPEC_ATTR(16, 2) SPEC_ATTR(8, 2) SPEC_ATTR(32, 2) SPEC_ATTR(32, 4)
+        SPEC_ATTR(32, 1)
+#ifndef MCB_DEV_BUILD   // (-DMCB_DEV_BUILD: only the default variant, for a quick compile while tuning)
+        SPEC_ATTR(16, 1) SPEC_ATTR(8, 1) SPEC_ATTR(16, 2) SPEC_ATTR(8, 2) SPEC_ATTR(32, 2) SPEC_ATTR(32, 4)
+#endif
 #undef SPEC_ATTR
 #undef SPEC_ATTR1
         if (rc) return fail(rc);
@@ -676,6 +680,9 @@ static void launch_run_spec_any(mcb_t *h, long long nsteps, long long *d_steps)
 {
     const int key = h->spec_gl * 10 + h->spec_w;
     switch (key) {
+#ifdef MCB_DEV_BUILD
+        default: launch_run_spec<COUL, 32, 1>(h, nsteps, d_steps); break;
+#else
         case 321: launch_run_spec<COUL, 32, 1>(h, nsteps, d_steps); break;
         case 322: launch_run_spec<COUL, 32, 2>(h, nsteps, d_steps); break;
         case 324: launch_run_spec<COUL, 32, 4>(h, nsteps, d_steps); break;
@@ -683,6 +690,7 @@ static void launch_run_spec_any(mcb_t *h, long long nsteps, long long *d_steps)
         case 162: launch_run_spec<COUL, 16, 2>(h, nsteps, d_steps); break;
         case 81: launch_run_spec<COUL, 8, 1>(h, nsteps, d_steps); break;
         default: launch_run_spec<COUL, 8, 2>(h, nsteps, d_steps); break;
+#endif
     }
 }
 

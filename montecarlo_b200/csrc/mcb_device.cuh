@@ -180,6 +180,12 @@ __device__ __forceinline__ void sincos_small(double x, double &sn, double &cs)
     cs = ((k + 1) & 2) ? -cc : cc;
 }
 
+// The same for any argument: first reduced to [-pi, pi] (the error of the reduction, |x| 2^-53, is that of forming x).
+__device__ __forceinline__ void sincos_any(double x, double &sn, double &cs)
+{
+    sincos_small(fma(-6.283185307179586, rint(x * 0.15915494309189535), x), sn, cs);
+}
+
 // Uniform stream (include/mcb200.h, mcb_seed_chains): u_n = (mix(key + (n+1) G) >> 11) * 2^-53, random access
 // in n; Metropolis step s (0-based) of a chain owns n = 8 s .. 8 s + 7.
 __device__ __forceinline__ unsigned long long mix64(unsigned long long x)

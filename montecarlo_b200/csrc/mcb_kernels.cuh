@@ -475,7 +475,49 @@ __global__ void __launch_bounds__(32) k_run_steps(Geo g, SiteRel rel, double *im
 // after).  The first step that fails the test, and everything behind it, is thrown away and re-evaluated in the
 // next batch with the same uniforms; a batch also ends at a step-size adaptation.  The resulting Markov chain
 // is the sequential one, decision for decision.  Only committed steps count as work.
-struct SpecX { double dE, esol, ncx, ncy, ncz; int i, nn, flags, pad; };   // what a step hands to the resolution
+// The ring of pre-drawn trial moves (k_run_spec): entry e = step & 63 holds the molecule pick, the six unit displacements
+// of randVec / randVecHoek before the step size (lib.f90:111-131), METROPOLIS' draw as log(u7)/log(E) - RV <= E**x with
+// x < 0 is log(RV)/log(E) <= x, and the left side needs only the uniform - and (sin, cos) of the three angle steps
+// dhoekmax * rv.  Both routines are deliberately NOT inlined: they run once per 32 steps / once per adaptation window,
+// and keeping their ~400 instructions out of the step loop is worth 3-5 % of the step (profiles/README.md, round 2).
+struct RingPtrs { double *thr, *rv; int *pick; double2 *sc; };
+
+__device__ __noinline__ void ring_draw(RingPtrs rg, unsigned long long key, unsigned long long sidx, int N, int quirk31, double dhoekmax)
+{
+    const int e = (int)(sidx & 63ULL);
+    const double u0 = stream_uniform(key, 8ULL * sidx);
+    int ii = (int)(u0 * (double)N) + 1;                     // MCINIT, MonteCarlo.F90:697-698
+    if (quirk31 && ii == 31) ii = 30;
+    rg.pick[e] = min(ii, N) - 1;
+#pragma unroll
+    for (int q = 0; q < 6; ++q) {
+        const double rvu = (stream_uniform(key, 8ULL * sidx + 1 + q) - 0.5) * 2.0;
+        rg.rv[6 * e + q] = (q < 3 ? INV_SQRT3 : 1.0) * rvu;
+    }
+    rg.thr[e] = log(stream_uniform(key, 8ULL * sidx + 7)) * (1.0 / LN_E_F32);
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        double sd, cd;
+        sincos_any(dhoekmax * rg.rv[6 * e + 3 + q], sd, cd);
+        rg.sc[3 * e + q] = make_double2(sd, cd);
+    }
+}
+
+// after a step-size adaptation: the pre-drawn steps [first, last) of the launch get the sin/cos of their angle steps at the new size
+__device__ __noinline__ void ring_rescale(RingPtrs rg, int ring0, int first, int last, int lane, double dhoekmax)
+{
+    for (int st = first + lane; st < last; st += 32) {
+        const int e = (ring0 + st) & 63;
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            double sd, cd;
+            sincos_any(dhoekmax * rg.rv[6 * e + 3 + q], sd, cd);
+            rg.sc[3 * e + q] = make_double2(sd, cd);
+        }
+    }
+}
+
+struct SpecX { double dE, ncx, ncy, ncz; int i, nn, flags, pad; };   // what a step hands to the resolution
 constexpr int SPECX_DOUBLES = sizeof(SpecX) / 8;
 
 // With W > 1 the block must still fit 7 times on an SM (1024 chains / 148 SMs): without the minimum-blocks hint the
@@ -522,9 +564,17 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
     double *const ring_thr = reinterpret_cast<double *>(xch) + (size_t)T * SPECX_DOUBLES;
     double *const ring_rv = ring_thr + 64;
     int *const ring_i = reinterpret_cast<int *>(ring_rv + 6 * 64);
-    // rowsum[j] = sum_i SS(i,j): what dE needs from the pair matrix.  Kept current on every accepted move, so the
-    // evaluation of a step never reads a matrix row (for large boxes that row lives in global memory).
-    double *const rowsum = ring_rv + 6 * 64 + 32;
+    // tot[j] = sum_i SS(i,j) + ENERGY(j): all that dE needs about the old state of molecule j.  Kept current on every
+    // accepted move, so the evaluation of a step never reads a matrix row (for large boxes that row lives in global
+    // memory) and never has to split the trial energy into its solvent and solute parts: ENERGY(:) itself is
+    // recomputed once, at the end of the launch, for the molecules that moved.
+    double *const tot = ring_rv + 6 * 64 + 32;
+    // sc[j] = (sin, cos) of molecule j's three Euler angles, ring_sc[e] = (sin, cos) of step e's three angle steps: the
+    // trial RotMatrix (lib.f90:52-57) then needs no sincos and no shuffle, only the angle-addition formulas
+    double2 *const sc = reinterpret_cast<double2 *>(tot + Np);                 // [N][3]
+    double2 *const ring_sc = sc + 3 * Np;                                        // [64][3]
+    unsigned *const movedw = reinterpret_cast<unsigned *>(ring_sc + 3 * 64);    // [nchunk]: molecules whose ENERGY is stale
+    const RingPtrs rg = {ring_thr, ring_rv, ring_i, ring_sc};
     ChainCtl s = ctl[c];
     for (int p = r; p < nsolp; p += GL) list[p] = N + p;
     __syncthreads();
@@ -538,14 +588,21 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
             a2 += mat[(size_t)(i + 2) * MS + j]; a3 += mat[(size_t)(i + 3) * MS + j];
         }
         for (; i < N; ++i) a0 += mat[(size_t)i * MS + j];
-        rowsum[j] = (a0 + a1) + (a2 + a3);
+        tot[j] = (a0 + a1) + (a2 + a3);
+        double sj, cj;
+#pragma unroll
+        for (int q = 0; q < 3; ++q) { sincos_any(hoek[q * Np + j], sj, cj); sc[3 * j + q] = make_double2(sj, cj); }
     }
+    for (int q = tid; q < nchunk; q += 32 * W) movedw[q] = 0u;
     __syncthreads();
     {
         double acc = 0.0;
-        for (int i = lane; i < N; i += 32) acc += fma(0.5, rowsum[i], energy[i]);
+        for (int i = lane; i < N; i += 32) acc += fma(0.5, tot[i], energy[i]);
         s.toteng = warp_sum(acc);
     }
+    __syncthreads();
+    for (int j = tid; j < N; j += 32 * W) tot[j] += energy[j];
+    __syncthreads();
     const double relx = rel.r[3 * a], rely = rel.r[3 * a + 1], relz = rel.r[3 * a + 2];
     const int wpair = rel.n_sites * rel.n_sites, wsol = rel.n_sites * g.nsol;
     const double neg_inv_rt = -1000.0 / (8.314 * s.temperature);
@@ -570,6 +627,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
     const int nsteps_i = (int)min(nsteps, (long long)0x3fffffff);
     int ring_hi = 0;                                                // the ring holds the launch-local steps [ring_hi - 64, ring_hi)
     const int ring0 = (int)(pos0 & 63ULL);
+    unsigned moved0 = 0u;                                           // SMALL: the molecules whose ENERGY is stale (a register; movedw otherwise)
     // launch-local index of the first production step: step0 + k + 1 >= start_prod (MonteCarlo.F90:760)
     const long long pf = s.start_prod - (long long)step0 - 1;
     const int prod_from = pf <= 0 ? 0 : (pf > 0x3fffffff ? 0x7fffffff : (int)pf);
@@ -580,21 +638,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
     while (done < nsteps_i) {
         // ================= pre-draw the next 32 steps when the ring runs low (one step per lane) =================
         while (done + T > ring_hi) {                                // (block-uniform condition; with W > 1 warp 0 fills for everybody)
-            if (W == 1 || warp == 0) {
-                const unsigned long long sidx = pos0 + (unsigned)(ring_hi + lane);
-                const int e = (int)(sidx & 63ULL);
-                const double u0 = stream_uniform(s.rng_key, 8ULL * sidx);
-                int ii = (int)(u0 * (double)N) + 1;                 // MCINIT, MonteCarlo.F90:697-698
-                if (g.quirk31 && ii == 31) ii = 30;
-                ring_i[e] = min(ii, N) - 1;
-#pragma unroll
-                for (int q = 0; q < 6; ++q) {                       // randVec / randVecHoek before the step size, lib.f90:111-131
-                    const double rvu = (stream_uniform(s.rng_key, 8ULL * sidx + 1 + q) - 0.5) * 2.0;
-                    ring_rv[6 * e + q] = (q < 3 ? INV_SQRT3 : 1.0) * rvu;
-                }
-                // METROPOLIS draws RV <= E**x; with x < 0 that is log(RV)/log(E) <= x, and the left side needs only the uniform
-                ring_thr[e] = log(stream_uniform(s.rng_key, 8ULL * sidx + 7)) * (1.0 / LN_E_F32);
-            }
+            if (W == 1 || warp == 0) ring_draw(rg, s.rng_key, pos0 + (unsigned)(ring_hi + lane), N, g.quirk31, s.dhoekmax);
             ring_hi += 32;
             if (W > 1) __syncthreads(); else __syncwarp();
         }
@@ -603,7 +647,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
         const int i = ring_i[ring_e];
         const double thr = ring_thr[ring_e];
         // sum of the old matrix row + ENERGY(i), straight from the running row sums
-        const double old_tot = rowsum[i] + energy[i];
+        const double old_tot = tot[i];
         const double old_part = r == 0 ? old_tot : 0.0;
         // the old matrix row itself is only needed if the move is accepted (row-sum bookkeeping); for up to 8 chunks
         // it is fetched now so that a global-memory row has arrived by then
@@ -621,11 +665,14 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
         }
         const double rv = (isang ? s.dhoekmax : s.dposmax) * ring_rv[6 * ring_e + rr];
         const double nv = wrap_fma(base[i] + rv, period, half, inv_half);       // :699-712
-        double sn, cs;
-        sincos_small(nv, sn, cs);
         const double ncx = shfl_d(nv, leader + 1), ncy = shfl_d(nv, leader + 2), ncz = shfl_d(nv, leader + 3);
-        const double c1 = shfl_d(cs, leader + 4), s1 = shfl_d(sn, leader + 4), c2 = shfl_d(cs, leader + 5),
-                     s2 = shfl_d(sn, leader + 5), c3 = shfl_d(cs, leader + 6), s3 = shfl_d(sn, leader + 6);
+        // sin and cos of the trial angles h + dh from those of h (cached per molecule) and of dh (pre-drawn): every lane
+        // forms all six itself.  (h + dh and its wrap, :700-707, are still formed exactly, above, for the stored angle.)
+        const double2 a1 = sc[3 * i], a2 = sc[3 * i + 1], a3 = sc[3 * i + 2];
+        const double2 d1 = ring_sc[3 * ring_e], d2 = ring_sc[3 * ring_e + 1], d3 = ring_sc[3 * ring_e + 2];
+        const double s1 = fma(a1.x, d1.y, a1.y * d1.x), c1 = fma(a1.y, d1.y, -(a1.x * d1.x));
+        const double s2 = fma(a2.x, d2.y, a2.y * d2.x), c2 = fma(a2.y, d2.y, -(a2.x * d2.x));
+        const double s3 = fma(a3.x, d3.y, a3.y * d3.x), c3 = fma(a3.y, d3.y, -(a3.x * d3.x));
         double sx, sy, sz;
         rotate_site(c1, s1, c2, s2, c3, s3, relx, rely, relz, ncx, ncy, ncz, sx, sy, sz);
         PH_T(0);
@@ -680,13 +727,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
         PH_T(2);
         // dE = sum(new row) - sum(old row) over the group; ENERGY(i) = the solute slots' share of it
         double dE = lane_tot - old_part;
-        double esol = 0.0;
         __syncwarp();
-        if (sub < nsolp) esol = epart[4 * sub + a];
-        if (nsolp > NSUB) {                                        // more than 4*NSUB solute atoms
-#pragma unroll 1
-            for (int p = sub + NSUB; p < nsolp; p += NSUB) esol += epart[4 * p + a];
-        }
         // One step per warp in a SMALL box: what an accepted move would write (new matrix entries and row sums of
         // the partners inside the cutoff, the row sums of those that left) does not depend on dE, so it is formed
         // here, in the shadow of the reduction's shuffles; the commit below is then only stores.
@@ -700,11 +741,11 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
             const int esl = c_has ? c_sl : 0;
             const double2 e01 = *reinterpret_cast<const double2 *>(epart + 4 * esl), e23 = *reinterpret_cast<const double2 *>(epart + 4 * esl + 2);
             c_e = (e01.x + e01.y) + (e23.x + e23.y);
-            c_rs_in = rowsum[c_j] + (c_e - mat[(size_t)i * MS + c_j]);
-            c_rs_left = rowsum[r < N ? r : 0] - oldrow[0];
+            c_rs_in = tot[c_j] + (c_e - mat[(size_t)i * MS + c_j]);
+            c_rs_left = tot[r < N ? r : 0] - oldrow[0];
         }
 #pragma unroll
-        for (int o = GL / 2; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
+        for (int o = GL / 2; o >= 1; o >>= 1) dE += shfl_xor_d(dE, o);
         // METROPOLIS (:720-788) on DELTA = dE
         const double exponent = dE * neg_inv_rt;
         const bool clamped = !(dE <= DBL_HUGE);                      // +Inf/NaN trial energy: clamped, rejected (:421-428); -Inf passes, as there
@@ -712,7 +753,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
         const bool accept = !clamped && (exponent >= 0.0 || (used8 && thr <= exponent));
         if (T > 1 && r == 0) {
             SpecX x;
-            x.dE = dE; x.esol = esol; x.ncx = ncx; x.ncy = ncy; x.ncz = ncz; x.i = i; x.nn = nn;
+            x.dE = dE; x.ncx = ncx; x.ncy = ncy; x.ncz = ncz; x.i = i; x.nn = nn;
             x.flags = (accept ? 1 : 0) | (used8 ? 2 : 0) | (clamped ? 4 : 0); x.pad = 0;
             xch[gidx] = x;
         }
@@ -751,14 +792,19 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
         for (int cg = 0; cg < T; ++cg) {
             if (HOIST) {
                 if (accept) {
-                    if (c_left) { rowsum[r] = c_rs_left; mat[(size_t)i * MS + r] = 0.0; mat[(size_t)r * MS + i] = 0.0; }
-                    if (c_has) { rowsum[c_j] = c_rs_in; mat[(size_t)i * MS + c_j] = c_e; mat[(size_t)c_j * MS + i] = c_e; }
+                    if (c_left) { tot[r] = c_rs_left; mat[(size_t)i * MS + r] = 0.0; mat[(size_t)r * MS + i] = 0.0; }
+                    if (c_has) { tot[c_j] = c_rs_in; mat[(size_t)i * MS + c_j] = c_e; mat[(size_t)c_j * MS + i] = c_e; }
                     if (r >= 1 && r <= 6) base[i] = nv;
                     if (r < 4) {
                         sites[SITE_DOUBLES * i + 3 * a] = sx; sites[SITE_DOUBLES * i + 3 * a + 1] = sy;
                         sites[SITE_DOUBLES * i + 3 * a + 2] = sz;
                     }
-                    if (r == 0) { energy[i] = esol; rowsum[i] = (dE + old_tot) - esol; }   // new row sum = new total - ENERGY(i)
+                    if (r == 0) tot[i] = dE + old_tot;
+                    // (three predicated stores from the values the rotation used: forming them again in the shadow of the
+                    // reduction, or under the accept branch, measured 4-8 % slower)
+                    if (r == 0) sc[3 * i] = make_double2(s1, c1);
+                    if (r == 1) sc[3 * i + 1] = make_double2(s2, c2);
+                    if (r == 2) sc[3 * i + 2] = make_double2(s3, c3);
                 }
             } else if (gidx == cg && gidx < progress && accept) {
                 // partners that left the cutoff: entry to zero, their row sums lose the old pair energy
@@ -772,7 +818,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
                             const int j = 32 * q + r + GL * m;
                             const double old = oldrow[q * MCH + m];
                             if (old != 0.0 && !((neww >> (r + GL * m)) & 1u)) {
-                                rowsum[j] -= old;
+                                tot[j] -= old;
                                 mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0;
                             }
                         }
@@ -785,7 +831,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
                             const int j = 32 * w0 + r + GL * m;
                             const double old = j < N ? mat[(size_t)i * MS + j] : 0.0;
                             if (old != 0.0 && !((neww >> (r + GL * m)) & 1u)) {
-                                rowsum[j] -= old;
+                                tot[j] -= old;
                                 mat[(size_t)i * MS + j] = 0.0; mat[(size_t)j * MS + i] = 0.0;
                             }
                         }
@@ -797,7 +843,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
                     const int j = list[sl];
                     const double2 e01 = *reinterpret_cast<const double2 *>(epart + 4 * sl), e23 = *reinterpret_cast<const double2 *>(epart + 4 * sl + 2);
                     const double e = (e01.x + e01.y) + (e23.x + e23.y);
-                    rowsum[j] += e - mat[(size_t)i * MS + j];
+                    tot[j] += e - mat[(size_t)i * MS + j];
                     mat[(size_t)i * MS + j] = e; mat[(size_t)j * MS + i] = e;
                     if (SMALL && GL == 32) break;
                 }
@@ -806,10 +852,15 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
                     sites[SITE_DOUBLES * i + 3 * a] = sx; sites[SITE_DOUBLES * i + 3 * a + 1] = sy;
                     sites[SITE_DOUBLES * i + 3 * a + 2] = sz;
                 }
-                if (r == 0) { energy[i] = esol; rowsum[i] = (dE + old_tot) - esol; }   // new row sum = new total - ENERGY(i)
+                if (r == 0) { tot[i] = dE + old_tot; if (!SMALL) movedw[i >> 5] |= 1u << (i & 31); }
+                if (r == 0) sc[3 * i] = make_double2(s1, c1);
+                if (r == 1) sc[3 * i + 1] = make_double2(s2, c2);
+                if (r == 2) sc[3 * i + 2] = make_double2(s3, c3);
+                if (SMALL) moved0 |= 1u << (i & 31);
             }
             if (T > 1) { if (W > 1) __syncthreads(); else __syncwarp(); }
         }
+        if (HOIST) moved0 |= accept ? 1u << (i & 31) : 0u;
         PH_T(6);
         // ================= bookkeeping in step order (every warp keeps the same copy) =================
 #pragma unroll
@@ -842,6 +893,7 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
             else if (ratio < 0.5) { s.dposmax *= (1.0 - s.padj); s.dhoekmax *= (1.0 - s.padj); }
             s.dposmax = fmax(s.dposmax, s.dposmin); s.dhoekmax = fmax(s.dhoekmax, s.dhoekmin);
             nacc = 0;
+            if (W == 1 || warp == 0) ring_rescale(rg, ring0, done + progress, ring_hi, lane, s.dhoekmax);
         }
         done += progress;
         if (W > 1) __syncthreads(); else __syncwarp();
@@ -850,6 +902,25 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
 #ifdef MCB_PHASE_CLOCKS
     if (tid == 0) for (int qq = 0; qq < 8; ++qq) atomicAdd(&g_phase[qq], (unsigned long long)ph[qq]);
 #endif
+    // ENERGY(i) (CalcLJ_SV, LennardJones.f90:89-148) of every molecule that moved, from its final cached sites: one
+    // (solute pseudo-molecule, own site) item per lane and pass, fixed summation order
+    if (SMALL) {   // (with several groups or warps per chain each commits its own step: merge the masks)
+        for (int o = 16; o >= 1; o >>= 1) moved0 |= __shfl_xor_sync(FULL, moved0, o);
+        if (lane == 0 && moved0) atomicOr(&movedw[0], moved0);
+    }
+    __syncthreads();
+    for (int i = warp; i < N; i += W) {
+        if (!((movedw[i >> 5] >> (i & 31)) & 1u)) continue;
+        double acc = 0.0;
+        for (int t = lane; t < 4 * nsolp; t += 32) {
+            const int p = t >> 2, as = t & 3;
+            acc += item_energy<COUL>(g, sites, tabAB, tabQ, N + p, 1 + p, as, sites[SITE_DOUBLES * i + 3 * as], sites[SITE_DOUBLES * i + 3 * as + 1],
+                                     sites[SITE_DOUBLES * i + 3 * as + 2]);
+        }
+        acc = warp_sum(acc);
+        if (lane == 0) energy[i] = acc;
+    }
+    __syncthreads();
     {
         const int n_mut = g.o_sites + SITE_DOUBLES * N;
         for (int qq = tid; qq < n_mut; qq += 32 * W) gimg[qq] = img[qq];
