@@ -21,7 +21,16 @@ module mcb200
   type, bind(C) :: mcb_chain_stats
     real(c_double) :: toteng, dposmax, dhoekmax, production, sum_e, sum_e2, ratio, last_delta
     integer(c_int64_t) :: step, nsuc, naccept, prod_acc, n_clamped, sitepairs, uniforms_used, n_stat
+    integer(c_int64_t) :: exch_attempts, exch_accepted
+    real(c_double) :: temperature
   end type
+
+  type, bind(C) :: mcb_global_stats      ! sums over a group of chains, over all ranks (mcb_reduce_stats)
+    real(c_double) :: sum_e, sum_e2, production, sum_toteng
+    integer(c_int64_t) :: n_stat, prod_acc, nsuc, step, sitepairs, n_clamped, uniforms_used, n_chains
+  end type
+
+  integer(c_int), parameter :: MCB_COMM_ID_BYTES = 128
 
   interface
     integer(c_int) function mcb_create(h, p) bind(C, name="mcb_create")
@@ -81,6 +90,42 @@ module mcb200
     end function
     integer(c_int) function mcb_reset_stats(h, chain0, nchains) bind(C, name="mcb_reset_stats")
       import; type(c_ptr), value :: h; integer(c_int), value :: chain0, nchains
+    end function
+    integer(c_int) function mcb_set_stream(h, cuda_stream) bind(C, name="mcb_set_stream")
+      import; type(c_ptr), value :: h, cuda_stream
+    end function
+    integer(c_int64_t) function mcb_launch_count(h) bind(C, name="mcb_launch_count")
+      import; type(c_ptr), value :: h
+    end function
+    integer(c_int) function mcb_measure_fp64_peak(device, ms, tflops) bind(C, name="mcb_measure_fp64_peak")
+      import; integer(c_int), value :: device; real(c_double), value :: ms; real(c_double), intent(out) :: tflops
+    end function
+    ! replica exchange between launches: pair_a, pair_b 0-based chain indices; uniforms and accepted may be c_null_ptr
+    integer(c_int) function mcb_exchange(h, npairs, pair_a, pair_b, uniforms, accepted) bind(C, name="mcb_exchange")
+      import; type(c_ptr), value :: h, uniforms, accepted; integer(c_int), value :: npairs
+      integer(c_int), intent(in) :: pair_a(*), pair_b(*)
+    end function
+    ! end of run: one NCCL all-reduce + one all-gather over the GPUs of the job (one handle per GPU / MPI rank)
+    integer(c_int) function mcb_comm_get_unique_id(id) bind(C, name="mcb_comm_get_unique_id")
+      import; character(kind=c_char), intent(out) :: id(MCB_COMM_ID_BYTES)
+    end function
+    integer(c_int) function mcb_comm_init(h, nranks, rank, id, n_total_chains) bind(C, name="mcb_comm_init")
+      import; type(c_ptr), value :: h; integer(c_int), value :: nranks, rank
+      character(kind=c_char), intent(in) :: id(MCB_COMM_ID_BYTES); integer(c_int64_t), value :: n_total_chains
+    end function
+    integer(c_int) function mcb_comm_attach(h, nccl_comm, nranks, rank, n_total_chains) bind(C, name="mcb_comm_attach")
+      import; type(c_ptr), value :: h, nccl_comm; integer(c_int), value :: nranks, rank; integer(c_int64_t), value :: n_total_chains
+    end function
+    integer(c_int) function mcb_comm_destroy(h) bind(C, name="mcb_comm_destroy")
+      import; type(c_ptr), value :: h
+    end function
+    integer(c_int) function mcb_reduce_stats(h, chains_per_group, out, n_groups) bind(C, name="mcb_reduce_stats")
+      import; type(c_ptr), value :: h; integer(c_int64_t), value :: chains_per_group; integer(c_int), value :: n_groups
+      type(mcb_global_stats), intent(out) :: out(*)
+    end function
+    integer(c_int) function mcb_gather_chains(h, out, n_total_chains) bind(C, name="mcb_gather_chains")
+      import; type(c_ptr), value :: h; integer(c_int64_t), value :: n_total_chains
+      real(c_double), intent(out) :: out(4, *)     ! (toteng, mean energy, acceptance, production mean) per global chain
     end function
     integer(c_int) function mcb_box_energy_noalloc(p, d_com, d_hoek, solute, sol_tab, d_out, stream, errbuf, errlen) &
         bind(C, name="mcb_box_energy_noalloc")   ! d_com, d_hoek, d_out: DEVICE pointers owned by the caller

@@ -77,6 +77,9 @@ typedef struct {
     int64_t sitepairs;      /* LJ_FORMULA evaluations of trial states (the unit of the throughput metric) */
     int64_t uniforms_used;
     int64_t n_stat;         /* number of terms in sum_e / sum_e2 */
+    int64_t exch_attempts;  /* replica-exchange attempts this chain took part in (mcb_exchange) */
+    int64_t exch_accepted;  /* ... and how many of them swapped its temperature */
+    double temperature;     /* the chain's current temperature (mcb_exchange moves it between chains) */
 } mcb_chain_stats;
 
 /* ---- life cycle --------------------------------------------------------------------------------- */
@@ -147,6 +150,22 @@ int mcb_get_stats(mcb_t *h, int chain0, int nchains, mcb_chain_stats *out);
 /* zero the counters (step, nsuc, production, ...) but keep coordinates, energies, step sizes and the position in
  * the built-in uniform stream */
 int mcb_reset_stats(mcb_t *h, int chain0, int nchains);
+
+/* ---- temperature ladder: replica exchange between launches ------------------------------------------ */
+/* The reference runs one temperature per process and has no exchange move; its acceptance rule is reused here
+ * (METROPOLIS, MonteCarlo.F90:728-744) for the standard parallel-tempering swap of two chains a, b:
+ *     EXPONENT = (1000/(8.314 T_a) - 1000/(8.314 T_b)) * (E_a - E_b)
+ *     EXPONENT < -75: rejected, no draw;  EXPONENT >= 0: accepted, no draw;  else accepted iff RV <= E**EXPONENT
+ * with E the reference's default-REAL 2.7182817 (lib.f90:17) and E_x the chains' current TOTENG.  An accepted swap
+ * exchanges the two chains' TEMPERATURES together with their step sizes DPOSMAX / DHOEKMAX (tuned per temperature);
+ * coordinates, energies and counters stay where they are.  pair_a[p], pair_b[p] are 0-based chain indices of this
+ * handle; a chain may appear in at most one pair per call.  uniforms[p] in [0,1) is pair p's RV (read only when the
+ * rule draws); with uniforms == NULL pair p draws from chain pair_a[p]'s exchange stream
+ *     key_x = mix(key + 0xD1B54A32D192ED03),  u_x(n) = (mix(key_x + (n+1)*G) >> 11) * 2^-53,
+ * n = draws that chain has made from it so far (key, mix, G as for mcb_seed_chains, which also rewinds n).
+ * accepted[p] (may be NULL) receives 1 or 0.  Both chains count the attempt in mcb_chain_stats.exch_attempts. */
+int mcb_exchange(mcb_t *h, int npairs, const int *pair_a, const int *pair_b, const double *uniforms,
+                 unsigned char *accepted);
 
 /* ---- end of run: one collective over the GPUs of the job ---------------------------------------------- */
 /* replaces: the way the reference combines its independent runs - separate processes whose logs PostProcess scrapes

@@ -45,7 +45,8 @@ class McbChainStats(C.Structure):
                 ("ratio", C.c_double), ("last_delta", C.c_double),
                 ("step", C.c_int64), ("nsuc", C.c_int64), ("naccept", C.c_int64), ("prod_acc", C.c_int64),
                 ("n_clamped", C.c_int64), ("sitepairs", C.c_int64), ("uniforms_used", C.c_int64),
-                ("n_stat", C.c_int64)]
+                ("n_stat", C.c_int64), ("exch_attempts", C.c_int64), ("exch_accepted", C.c_int64),
+                ("temperature", C.c_double)]
 
 
 class McbGlobalStats(C.Structure):
@@ -76,6 +77,7 @@ SIGNATURES = {
     "mcb_run_steps": (C.c_int, [C.c_void_p, C.c_int64, _dp, C.c_int64, _i64p, _i64p]),
     "mcb_get_stats": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(McbChainStats)]),
     "mcb_reset_stats": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "mcb_exchange": (C.c_int, [C.c_void_p, C.c_int, _ip, _ip, _dp, _u8p]),
     "mcb_measure_fp64_peak": (C.c_int, [C.c_int, C.c_double, _dp]),
     "mcb_comm_get_unique_id": (C.c_int, [C.c_char_p]),
     "mcb_comm_init": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_char_p, C.c_int64]),

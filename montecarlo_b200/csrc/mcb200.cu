@@ -616,7 +616,7 @@ extern "C" int mcb_seed_chains(mcb_t *h, int chain0, int nchains, const uint64_t
     for (int c = 0; c < nchains; ++c) {
         unsigned long long x = seeds[c] + 0x9E3779B97F4A7C15ULL;
         x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL; x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL; x ^= x >> 31;
-        ctl[c].rng_key = x; ctl[c].rng_n = 0;
+        ctl[c].rng_key = x; ctl[c].rng_n = 0; ctl[c].xn = 0;
     }
     return store_ctl(h, chain0, nchains, ctl);
 }
@@ -629,6 +629,7 @@ extern "C" int mcb_reset_stats(mcb_t *h, int chain0, int nchains)
     for (auto &s : ctl) {
         s.production = s.sum_e = s.sum_e2 = s.ratio = s.last_delta = 0.0;
         s.step = s.nsuc = s.naccept = s.prod_acc = s.nclamp = s.sitepairs = s.uused = s.nstat = 0;
+        s.xatt = s.xacc = 0;
     }
     return store_ctl(h, chain0, nchains, ctl);
 }
@@ -647,7 +648,65 @@ extern "C" int mcb_get_stats(mcb_t *h, int chain0, int nchains, mcb_chain_stats 
         o.sum_e = s.sum_e; o.sum_e2 = s.sum_e2; o.ratio = s.ratio; o.last_delta = s.last_delta;
         o.step = s.step; o.nsuc = s.nsuc; o.naccept = s.naccept; o.prod_acc = s.prod_acc; o.n_clamped = s.nclamp;
         o.sitepairs = s.sitepairs; o.uniforms_used = s.uused; o.n_stat = s.nstat;
+        o.exch_attempts = s.xatt; o.exch_accepted = s.xacc; o.temperature = s.temperature;
     }
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ replica exchange
+// One thread per pair; the rule is METROPOLIS' (MonteCarlo.F90:728-744) applied to the parallel-tempering exponent.
+__global__ void k_exchange(ChainCtl *ctl, int npairs, const int *pa, const int *pb, const double *u, unsigned char *acc)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npairs) return;
+    ChainCtl &A = ctl[pa[p]], &B = ctl[pb[p]];
+    const double ba = 1000.0 / (8.314 * A.temperature), bb = 1000.0 / (8.314 * B.temperature);
+    const double exponent = (ba - bb) * (A.toteng - B.toteng);
+    bool accept;
+    if (exponent < -75.0) accept = false;                       // KANS = 0, RV = 1: no draw (:730-733)
+    else if (exponent >= 0.0) accept = true;                    // KANS = 1, RV = 0: no draw (:734-736)
+    else {
+        double rv;
+        if (u) rv = u[p];
+        else { rv = stream_uniform(mix64(A.rng_key + 0xD1B54A32D192ED03ULL), A.xn); A.xn += 1; }
+        accept = rv <= fmin(exp(exponent * LN_E_F32), 1.0);    // KANS = E**EXPONENT, RV <= KANS (:738-744)
+    }
+    A.xatt += 1; B.xatt += 1;
+    if (accept) {
+        double t;
+        t = A.temperature; A.temperature = B.temperature; B.temperature = t;
+        t = A.dposmax; A.dposmax = B.dposmax; B.dposmax = t;
+        t = A.dhoekmax; A.dhoekmax = B.dhoekmax; B.dhoekmax = t;
+        A.xacc += 1; B.xacc += 1;
+    }
+    if (acc) acc[p] = accept ? 1 : 0;
+}
+
+extern "C" int mcb_exchange(mcb_t *h, int npairs, const int *pair_a, const int *pair_b, const double *uniforms, unsigned char *accepted)
+{
+    if (!h) return 1;
+    if (npairs < 0 || (npairs > 0 && (!pair_a || !pair_b))) return arg_err(h, "mcb_exchange: null pair arrays");
+    if (npairs == 0) return 0;
+    std::vector<char> seen(h->n_chains, 0);
+    for (int p = 0; p < npairs; ++p) {
+        const int a = pair_a[p], b = pair_b[p];
+        if (a < 0 || b < 0 || a >= h->n_chains || b >= h->n_chains || a == b || seen[a] || seen[b])
+            return arg_err(h, "mcb_exchange: pairs must be distinct chains of this handle, each chain in at most one pair");
+        seen[a] = seen[b] = 1;
+    }
+    CK(h, cudaSetDevice(h->device));
+    if (int rc = ensure_prepared(h)) return rc;     // TOTENG must be current
+    // inputs ride in the staging buffers of the single-step entry points: d_rsolv [n_chains] ints is too small for two
+    // index arrays, so the pairs go through d_ll (2 x n_chains 64-bit words) and the uniforms through d_out
+    int *d_a = reinterpret_cast<int *>(h->d_ll), *d_b = d_a + h->n_chains;
+    CK(h, cudaMemcpyAsync(d_a, pair_a, sizeof(int) * npairs, cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaMemcpyAsync(d_b, pair_b, sizeof(int) * npairs, cudaMemcpyHostToDevice, h->stream));
+    if (uniforms) CK(h, cudaMemcpyAsync(h->d_out, uniforms, sizeof(double) * npairs, cudaMemcpyHostToDevice, h->stream));
+    k_exchange<<<(npairs + 127) / 128, 128, 0, h->stream>>>(h->ctl, npairs, d_a, d_b, uniforms ? h->d_out : nullptr, accepted ? h->d_acc : nullptr);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    if (accepted) CK(h, cudaMemcpyAsync(accepted, h->d_acc, npairs, cudaMemcpyDeviceToHost, h->stream));
+    CK(h, cudaStreamSynchronize(h->stream));
     return 0;
 }
 

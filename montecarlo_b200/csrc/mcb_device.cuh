@@ -50,6 +50,8 @@ struct ChainCtl {
     double temperature, dposmin, dhoekmin, padj;
     long long start_prod;
     int nadj, energies_valid;
+    long long xatt, xacc;          // replica-exchange attempts / acceptances this chain took part in (mcb_exchange)
+    unsigned long long xn;         // position in the chain's exchange stream
 };
 
 struct ChainPtrs {

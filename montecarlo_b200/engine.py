@@ -181,6 +181,20 @@ class LJEngine:
         chain0, nchains = self._range(chain0, nchains)
         self._ck(self.lib.mcb_reset_stats(self.h, chain0, nchains), "mcb_reset_stats")
 
+    def exchange(self, pair_a, pair_b, uniforms=None):
+        """Replica exchange between launches: the reference's METROPOLIS rule (MonteCarlo.F90:728-744) on the
+        parallel-tempering exponent; an accepted pair swaps temperatures and step sizes.  Returns accepted[p]."""
+        pa = np.ascontiguousarray(pair_a, dtype=np.int32); pb = np.ascontiguousarray(pair_b, dtype=np.int32)
+        n = int(pa.shape[0])
+        assert pb.shape == pa.shape
+        u = None if uniforms is None else np.ascontiguousarray(uniforms, dtype=np.float64)
+        assert u is None or u.shape == (n,)
+        acc = np.zeros(n, dtype=np.uint8)
+        ip = C.POINTER(C.c_int)
+        self._ck(self.lib.mcb_exchange(self.h, n, pa.ctypes.data_as(ip), pb.ctypes.data_as(ip), _d(u),
+                                       acc.ctypes.data_as(C.POINTER(C.c_ubyte))), "mcb_exchange")
+        return acc.astype(bool)
+
     def stats(self, chain0: int = 0, nchains: int | None = None) -> dict:
         chain0, nchains = self._range(chain0, nchains)
         arr = (McbChainStats * nchains)()

@@ -657,6 +657,42 @@ int64_t mco_run_steps_rng(mco_chain *c, int64_t nsteps, uint64_t rng[2], double 
     return nsteps;
 }
 
+/* ------------------------------------------------------------------ replica exchange (no counterpart in the reference)
+ * The reference has one temperature per process and no exchange move.  The product's mcb_exchange applies the
+ * reference's own acceptance rule, METROPOLIS (MonteCarlo.F90:728-744), to the parallel-tempering exponent
+ * (beta_a - beta_b)(E_a - E_b), beta = 1000/(8.314 T); this is that rule, literally, for two chains.  An accepted swap
+ * exchanges the temperatures and the step sizes.  *used = 1 if u was consumed.  Returns 1 if accepted. */
+int mco_exchange(mco_chain *a, mco_chain *b, double u, int *used)
+{
+    REAL ba = (REAL)1000.0 / ((REAL)8.314 * a->temperature), bb = (REAL)1000.0 / ((REAL)8.314 * b->temperature);
+    REAL exponent = (ba - bb) * (a->toteng - b->toteng);
+    REAL kans, rv;
+    int drew = 0;
+    if (exponent < (REAL)-75.0) { kans = 0; rv = 1; }            /* :730-733 */
+    else if (exponent >= 0) { kans = 1; rv = 0; }                /* :734-736 */
+    else {
+        kans = R_POW((REAL)mco_const_e(), exponent);             /* :738 */
+        rv = u; drew = 1;                                        /* :739 */
+        if (kans > 1) kans = 1;
+    }
+    if (used) *used = drew;
+    if (!(rv <= kans)) return 0;                                 /* :744 */
+    REAL t;
+    t = a->temperature; a->temperature = b->temperature; b->temperature = t;
+    t = a->dposmax; a->dposmax = b->dposmax; b->dposmax = t;
+    t = a->dhoekmax; a->dhoekmax = b->dhoekmax; b->dhoekmax = t;
+    return 1;
+}
+
+/* the exchange stream of a chain seeded with `seed` (include/mcb200.h, mcb_exchange): key_x = mix(key + C), state = {key_x, n} */
+void mco_rng_exchange_seed(uint64_t s[2], uint64_t seed)
+{
+    s[0] = mix64(mix64(seed + 0x9E3779B97F4A7C15ULL) + 0xD1B54A32D192ED03ULL);
+    s[1] = 0;
+}
+
+double mco_get_temperature(const mco_chain *c) { return (double)c->temperature; }
+
 void mco_get_stats(const mco_chain *c, double out[12])
 {
     out[0] = (double)c->step; out[1] = (double)c->nsuc; out[2] = (double)c->naccept; out[3] = (double)c->prod_acc;

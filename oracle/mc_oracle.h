@@ -85,6 +85,11 @@ int64_t mco_run_steps(mco_chain *c, int64_t nsteps, const double *uniforms, int6
 /* nsteps steps fed from the built-in counter stream: step s (0-based, chain life) owns u(8s)..u(8s+7) */
 int64_t mco_run_steps_rng(mco_chain *c, int64_t nsteps, uint64_t rng[2], double *trace);
 
+/* ---- replica exchange: no counterpart in the reference; its METROPOLIS rule (:728-744) on (beta_a - beta_b)(E_a - E_b) ---- */
+int mco_exchange(mco_chain *a, mco_chain *b, double u, int *used);
+void mco_rng_exchange_seed(uint64_t state[2], uint64_t seed);
+double mco_get_temperature(const mco_chain *c);
+
 /* counters: {step, nsuc, naccept_window, prod_acc, n_clamped, sitepairs(lo), toteng, toteng_old, production,
  *            dposmax, dhoekmax} */
 void mco_get_stats(const mco_chain *c, double out[12]);

@@ -65,6 +65,11 @@ def _load(name: str):
     lib.mco_rng_seed.argtypes = [_u64p, C.c_uint64]
     lib.mco_rng_uniform.restype = C.c_double
     lib.mco_rng_uniform.argtypes = [_u64p]
+    lib.mco_exchange.restype = C.c_int
+    lib.mco_exchange.argtypes = [C.c_void_p, C.c_void_p, C.c_double, _ip]
+    lib.mco_rng_exchange_seed.argtypes = [_u64p, C.c_uint64]
+    lib.mco_get_temperature.restype = C.c_double
+    lib.mco_get_temperature.argtypes = [C.c_void_p]
     lib.mco_rotmatrix.argtypes = [_dp, _dp, _dp, C.c_int, _dp]
     lib.mco_lj_formula.argtypes = [C.c_double] * 6 + [_dp, C.c_double, C.c_double, _dp]
     for n in ("pi", "tau", "e", "hartree2kjmol", "conv_reference", "conv_intended"):
@@ -173,6 +178,19 @@ class OracleChain:
         out = np.zeros(12)
         self.L.mco_get_stats(self.h, _ptr(out))
         return dict(zip(STAT_COLS, out))
+
+
+def exchange(oa: "OracleChain", ob: "OracleChain", u: float):
+    """The exchange rule on two oracle chains; returns (accepted, used_the_uniform)."""
+    used = C.c_int(0)
+    acc = oa.L.mco_exchange(oa.h, ob.h, float(u), C.byref(used))
+    return bool(acc), bool(used.value)
+
+
+def rng_exchange_seed(seed: int) -> np.ndarray:
+    s = np.zeros(2, dtype=np.uint64)
+    lib().mco_rng_exchange_seed(_ptr(s, _u64p), C.c_uint64(seed))
+    return s
 
 
 def rng_seed(seed: int) -> np.ndarray:

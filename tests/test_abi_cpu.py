@@ -27,11 +27,23 @@ def test_header_and_bindings_agree(lib):
         assert getattr(lib, name) is not None
 
 
+def test_fortran_binding_covers_the_header():
+    """bindings/mcb200.f90 (compile-unverified here: no Fortran compiler) binds every symbol the header declares,
+    and INTEGRATION.md prints that same module."""
+    header = (ROOT / "include" / "mcb200.h").read_text()
+    f90 = (ROOT / "bindings" / "mcb200.f90").read_text()
+    declared = set(re.findall(r"\b(mcb_[a-z0-9_]+)\s*\(", header))
+    bound = set(re.findall(r'name="(mcb_[a-z0-9_]+)"', f90))
+    assert declared == bound, declared ^ bound
+    module = f90[f90.index("module mcb200"):]
+    assert module in (ROOT / "INTEGRATION.md").read_text()
+
+
 def test_struct_layouts_match_header():
     from montecarlo_b200._lib import McbChainStats, McbMcParams, McbParams
     assert C.sizeof(McbParams) == 8 * 4 + 3 * 8 + 2 * 8
     assert C.sizeof(McbMcParams) == 6 * 8 + 2 * 4 + 8
-    assert C.sizeof(McbChainStats) == 16 * 8
+    assert C.sizeof(McbChainStats) == 19 * 8
     from montecarlo_b200._lib import McbGlobalStats, COMM_ID_BYTES
     assert C.sizeof(McbGlobalStats) == 12 * 8 and COMM_ID_BYTES == 128
 

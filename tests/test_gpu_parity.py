@@ -502,6 +502,15 @@ def test_config4_dihedral_sweep(shipped):
     assert np.all(e0 == e0[:, :1]) and len(np.unique(np.round(e0[:, 0], 6))) == 36   # same conformer, same start energy
     per_angle_mean = (st["sum_e"] / st["n_stat"]).reshape(-1, per).mean(axis=1)
     assert per_angle_mean.shape == (36,) and np.all(np.isfinite(per_angle_mean))
+    # the end-of-run collective per angle (one group per conformer) and what consumes it: the reference's window hopping
+    # (PostProcess.F90:260-304) over the gathered per-chain mean energies, one "run" per chain index inside an angle
+    g = eng.reduce_stats(per)
+    assert list(g["n_chains"]) == [per] * 36 and np.allclose(g["mean_e"], (st["sum_e"].reshape(-1, per).sum(axis=1) / st["n_stat"].reshape(-1, per).sum(axis=1)), rtol=1e-13)
+    from montecarlo_b200 import postprocess
+    e_run_win = eng.gather_chains()["mean_e"].reshape(36, per).T.copy()          # [run, window]
+    rng = np.random.default_rng(11)
+    old, now, acc = postprocess.window_hopping(e_run_win, 300.0, iter(rng.random(4 * per)))
+    assert old[0] == int(np.argmin(e_run_win[0])) and np.all((now - old) % 36 % 34 == 1) and len(acc) == per
 
 
 def test_quirk_31_and_odd_sizes(shipped):
@@ -860,3 +869,54 @@ def test_row_energy_refuses_while_a_trial_is_pending(shipped):
     o = ol.OracleChain(system, com[0], hoek[0])
     _, orow, oei = o.row_energy(2)
     assert _close(row, orow, scale=np.abs(orow) + 1e-3) and _close(ei, oei)
+
+
+@pytest.mark.parametrize("stream", ["caller", "builtin"])
+def test_replica_exchange_ladder(shipped, stream):
+    """Temperature ladder with exchange moves between launches (mcb_exchange): eight chains at 250..600 K, rounds of
+    300 steps, even pairs then odd pairs; every decision, every temperature and the chains afterwards must be those of
+    the oracle applying the same rule (the reference's METROPOLIS, MonteCarlo.F90:728-744) with the same uniforms."""
+    box, system = shipped
+    nch, rounds, nsteps = 8, 10, 300
+    temps = np.linspace(250.0, 600.0, nch)
+    seeds = np.arange(501, 501 + nch, dtype=np.uint64)
+    eng = _engine(system, box.n, n_chains=nch)
+    eng.set_state(box.com, box.hoek)
+    eng.seed(seeds)
+    eng.set_mc_params(temperature=temps)
+    eng.total_energy()
+    orc = []
+    for c in range(nch):
+        o = ol.OracleChain(system, box.com, box.hoek)
+        o.set_mc_params(temperature=temps[c])
+        o.total_energy()
+        orc.append((o, ol.rng_seed(int(seeds[c])), ol.rng_exchange_seed(int(seeds[c]))))
+    rng = np.random.default_rng(2026)
+    n_acc = n_draw = 0
+    for rd in range(rounds):
+        eng.run_steps(nsteps)
+        for o, st, _ in orc:
+            # the oracle keeps Metropolis parameters per chain; only temperature and step sizes move in an exchange
+            o.run_steps_rng(nsteps, st, trace=False)
+        pa = np.arange(rd % 2, nch - 1, 2); pb = pa + 1
+        u = rng.random(len(pa)) if stream == "caller" else None
+        acc = eng.exchange(pa, pb, u)
+        for p, (a, b) in enumerate(zip(pa, pb)):
+            uu = u[p] if u is not None else float(ol.rng_uniforms(orc[a][2].copy(), 1)[0])
+            oacc, used = ol.exchange(orc[a][0], orc[b][0], uu)
+            if used and u is None:
+                ol.rng_uniforms(orc[a][2], 1)          # the draw advances chain a's exchange stream
+            assert oacc == acc[p], (rd, p)
+            n_acc += oacc; n_draw += used
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    assert n_acc > 5 and n_draw > 5 and st["exch_accepted"].sum() == 2 * n_acc
+    assert st["exch_attempts"].sum() == 2 * sum(len(np.arange(rd % 2, nch - 1, 2)) for rd in range(rounds))
+    assert sorted(st["temperature"]) == sorted(temps)                       # a permutation of the ladder
+    for c in range(nch):
+        o = orc[c][0]
+        assert st["temperature"][c] == o.L.mco_get_temperature(o.h)
+        _compare_chain(st, c, o.stats(), com, hoek, o)
+    from montecarlo_b200.engine import McbError
+    with pytest.raises(McbError, match="at most one pair"):
+        eng.exchange([0, 1], [1, 2])

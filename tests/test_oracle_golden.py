@@ -161,3 +161,33 @@ def test_rng_stream_is_documented():
     a = ol.rng_uniforms(ol.rng_seed(1), 4096)
     b = ol.rng_uniforms(ol.rng_seed(2), 4096)
     assert abs(a.mean() - 0.5) < 0.02 and abs(np.corrcoef(a, b)[0, 1]) < 0.06
+
+
+def test_exchange_rule_is_metropolis_rule(shipped):
+    """mco_exchange (the checker for mcb_exchange; the reference has no exchange move) is METROPOLIS' rule
+    (MonteCarlo.F90:728-744) on (beta_a - beta_b)(E_a - E_b): no draw below -75 and at or above 0, else RV <= E**x with
+    the default-REAL E; an accepted swap moves temperature and step sizes, nothing else."""
+    box, system = shipped
+    com2 = box.com.copy(); com2[0] += 0.05
+    a = ol.OracleChain(system, box.com, box.hoek); b = ol.OracleChain(system, com2, box.hoek)
+    a.set_mc_params(temperature=300.0, dposmax=0.3); b.set_mc_params(temperature=330.0, dposmax=0.4)
+    ea, eb = a.total_energy(), b.total_energy()
+    x = (1000.0 / (8.314 * 300.0) - 1000.0 / (8.314 * 330.0)) * (ea - eb)
+    assert -75.0 < x and x != 0.0
+    if x >= 0.0:
+        assert ol.exchange(a, b, 0.999999) == (True, False)
+    else:
+        kans = ol.lib().mco_const_e() ** x
+        assert ol.exchange(a, b, float(np.nextafter(kans, 1.0))) == (False, True)      # RV just above KANS: rejected
+        assert a.L.mco_get_temperature(a.h) == 300.0
+        assert ol.exchange(a, b, kans) == (True, True)                                  # RV == KANS: accepted (.LE.)
+    assert a.L.mco_get_temperature(a.h) == 330.0 and b.L.mco_get_temperature(b.h) == 300.0
+    assert a.stats()["dposmax"] == 0.4 and b.stats()["dposmax"] == 0.3
+    assert a.stats()["toteng"] == ea and b.stats()["toteng"] == eb
+    # a hopeless swap (exponent < -75) never draws
+    c = ol.OracleChain(system, box.com, box.hoek); d = ol.OracleChain(system, com2, box.hoek)
+    ec, ed = c.total_energy(), d.total_energy()
+    cold, hot = (c, d) if ec < ed else (d, c)                     # the cold chain already holds the lower energy
+    cold.set_mc_params(temperature=1.0); hot.set_mc_params(temperature=1000.0)
+    cold.total_energy(); hot.total_energy()
+    assert ol.exchange(cold, hot, 0.0) == (False, False) and ol.exchange(hot, cold, 0.0) == (False, False)

@@ -29,3 +29,46 @@ def test_window_hopping_sequence():
     # cyclic neighbours
     old, now, acc = pp.window_hopping(np.array([[0.0, 1.0, 1.0]]), 300.0, iter([0.9, 0.0]))
     assert old[0] == 0 and now[0] == 2
+
+
+def test_window_hopping_literal_indexing():
+    """literal=True reproduces COMPARE's transposed subscripts (PostProcess.F90:66, :249, :277): ENERGY(I, NEXT) on an
+    array allocated ENERGY(NUMLOG, RUNS) is the column-major linear element NEXT*NUMLOG + I.  Checked against an
+    independent emulation with a Fortran-ordered numpy array."""
+    rng = np.random.default_rng(4)
+    nwin, runs = 3, 7
+    e = rng.normal(0.0, 2.0, size=(runs, nwin))               # [run, window]
+    F = np.asfortranarray(e.T)                                # ENERGY(NUMLOG, RUNS), column-major like the reference
+    lin = F.ravel(order="F")
+
+    def emulate(uniforms):
+        it = iter(uniforms)
+        cur = int(np.argmin(F[:, 0])); out = []
+        for i in range(runs):
+            nxt = cur + 1 if next(it) < 0.5 else cur - 1
+            nxt = 0 if nxt > nwin - 1 else (nwin - 1 if nxt < 0 else nxt)
+            k_n, k_c = nxt * nwin + i, cur * nwin + i          # element (I, NEXT) of an array with leading dimension NUMLOG
+            if max(k_n, k_c) >= lin.size:
+                return out, i
+            x = -1.0 * (lin[k_n] - lin[k_c]) * 1000.0 / (8.314 * 300.0)
+            if x < -75.0: kans, rv = 0.0, 1.0
+            elif x >= 0.0: kans, rv = 1.0, 0.0
+            else: kans, rv = min(np.exp(x), 1.0), next(it)
+            a = rv < kans
+            out.append((cur, nxt, a))
+            if a: cur = nxt
+        return out, runs
+
+    u = list(rng.random(4 * runs))
+    want, n_ok = emulate(u)
+    old, now, acc = pp.window_hopping(e, 300.0, iter(u), literal=True)
+    assert [(int(o), int(n), bool(a)) for o, n, a in zip(old, now, acc)] == want
+    o2, n2, a2 = pp.window_hopping(e, 300.0, iter(u), literal=False)
+    assert not (np.array_equal(acc, a2) and np.array_equal(now, n2))          # (on this data the intended reading hops differently)
+    assert n_ok == runs
+    # the two readings differ: run 3's literal element (window 1) is linear 1*3 + 3 = 6 = ENERGY(1, 3) = run 2, window 0
+    assert lin[1 * nwin + 3] == e[2, 0]
+    # fewer runs than windows: the literal read leaves the array (undefined in the reference)
+    import pytest
+    with pytest.raises(IndexError, match="outside ENERGY"):
+        pp.window_hopping(np.zeros((2, 3)), 300.0, iter([0.9] + [0.2] * 8), literal=True)   # first hop: window 0 -> 2
