@@ -302,6 +302,7 @@ def run_gpu_arm(args):
     join_comm(eng, nch * world)
     m1 = measure_leg(eng, system, box, nch, S, args.steps, args.warmup, seeds, stream, flush, barrier, torch)
     # the path's one collective, inside the product: all-reduce of the statistics + all-gather of per-chain finals
+    eng.reduce_stats()        # (the first collective of a new communicator also sets up its connections: untimed)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     a.record(stream)

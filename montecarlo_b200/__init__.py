@@ -8,6 +8,7 @@ from . import boxio  # noqa: F401
 
 def __getattr__(name):  # engine needs the built CUDA library; keep `import montecarlo_b200` cheap
     if name in ("LJEngine", "McbError", "measure_fp64_peak", "engine"):
-        from . import engine
+        import importlib
+        engine = importlib.import_module(".engine", __name__)   # (not `from . import`: that asks __getattr__ again)
         return engine if name == "engine" else getattr(engine, name)
     raise AttributeError(name)

@@ -207,6 +207,7 @@ class LJEngine:
     def comm_init(self, nranks: int, rank: int, unique_id: bytes, n_total_chains: int):
         """Join the job's NCCL communicator; `unique_id` are the 128 bytes rank 0 got from comm_unique_id()."""
         assert len(unique_id) == _lib.COMM_ID_BYTES
+        _preload_nccl()
         self._ck(self.lib.mcb_comm_init(self.h, int(nranks), int(rank), unique_id, int(n_total_chains)), "mcb_comm_init")
         self._n_total = int(n_total_chains)
 
@@ -239,8 +240,34 @@ class LJEngine:
                 "production_mean": out[:, 3].copy()}
 
 
+_NCCL_PRELOADED = False
+
+
+def _preload_nccl():
+    """Python hosts only.  libmcb200.so binds NCCL by soname at first use and reuses a copy the process has already
+    loaded.  If PyTorch is imported LATER in the same process it would then be handed that copy too (same soname) and
+    fail on symbols newer than the system NCCL has.  So before the library's first NCCL call, load the copy PyTorch
+    ships (the `nvidia.nccl` wheel) when there is one; the library picks it up, and a later `import torch` is unaffected."""
+    global _NCCL_PRELOADED
+    if _NCCL_PRELOADED:
+        return
+    _NCCL_PRELOADED = True
+    try:
+        import importlib.util
+        from pathlib import Path as _P
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for loc in (spec.submodule_search_locations if spec else []):
+            cand = _P(loc) / "lib" / "libnccl.so.2"
+            if cand.exists():
+                C.CDLL(str(cand), mode=C.RTLD_GLOBAL)
+                return
+    except (ImportError, OSError, ValueError):
+        pass
+
+
 def comm_unique_id() -> bytes:
     """The 128-byte NCCL id rank 0 creates and hands to the other ranks (by MPI, a file, torch.distributed ...)."""
+    _preload_nccl()
     lib = _lib.load()
     buf = C.create_string_buffer(_lib.COMM_ID_BYTES)
     rc = lib.mcb_comm_get_unique_id(buf)
