@@ -86,8 +86,11 @@ __device__ __forceinline__ double warp_sum(double v)
 //     |R - BOXL2*AINT(R/BOXL)| = | |R| - BOXL2*floor(|R|/BOXL) |
 // and floor comes from one round-down FMA onto 2^52 (whose ulp is 1) instead of an fp64 FRND, which on B200
 // issues once per ~13 cycles per warp (tools/latency.cu) and would cost as much as all the DFMAs of a site pair.
-// The quotient uses the reciprocal of BOXL: it can pick the other image only when |R|/BOXL is within an ulp
-// of an integer, where both images are equally far (to 1e-15), so r^2 and the energy do not notice.
+// The quotient uses the reciprocal of BOXL, so floor can differ from the reference's AINT(R/BOXL) only when
+// |R|/BOXL lies within an ulp of an integer - a set of measure ~1e-16 per component, not a harmless one: at an odd
+// quotient the two candidates are the two equally distant images (r^2 unchanged to 1e-15), but at an EVEN quotient
+// (|R| = 2*BOXL, reachable: see above) they are |R| ~ 0 and |R| ~ 2*BOXL, a different energy.  The argument for
+// accepting it is the probability, not equidistance; SURVEY.md section 7 takes the same view.
 __device__ __forceinline__ double mic_abs(double d, const Geo &g)
 {
     const double a = fabs(d);

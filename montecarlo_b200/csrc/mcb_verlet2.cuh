@@ -297,8 +297,12 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
             const int nslots = nsolp + nn;
             double lane_tot = 0.0;
             if (use_list) {
-                for (int sb = 0; sb < nslots; sb += 2 * 8)   // the same number of passes on every lane
+                // passes of two items per lane, a remainder of at most 8 slots in a pass of one (as k_run_spec)
+                int sb = 0;
+                for (; nslots - sb > 8; sb += 2 * 8)
                     lane_tot += items_staged<COUL, 2>(g, sites, tabAB, tabQ, list, nsolp, nslots, sb + sub, 8, a, sx, sy, sz, epart);
+                if (sb < nslots)
+                    lane_tot += items_staged<COUL, 1>(g, sites, tabAB, tabQ, list, nsolp, nslots, sb + sub, 8, a, sx, sy, sz, epart);
             } else {
                 for (int sb = 0; sb < nslots; sb += 2 * 8)
                     lane_tot += items_staged<COUL, 2>(g, sites, tabAB, tabQ, list_g, nsolp, nslots, sb + sub, 8, a, sx, sy, sz, epart_g);
