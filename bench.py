@@ -234,7 +234,10 @@ def measure_leg(eng, system, box, nch, S, steps, warmup, seeds, stream, flush, b
            "t": sum(kernel_ms) * 1e-3}
     # ---- end to end through the C ABI with host buffers: H2D of every chain's CoM/HOEK, K-step launch,
     #      D2H of the statistics and of the final coordinates (what the driver's dump/result writers read)
-    com_h, hoek_h = eng.get_state()
+    # the host buffers are page-locked, as the harness contract asks (a driver would cudaHostRegister its arrays)
+    com_h = torch.empty((nch, box.n, 3), dtype=torch.float64, pin_memory=True).numpy()
+    hoek_h = torch.empty((nch, box.n, 3), dtype=torch.float64, pin_memory=True).numpy()
+    eng.get_state(out=(com_h, hoek_h))
     e2e_ms, w_e2e = [], 0.0
     out["h2d"] = com_h.nbytes + hoek_h.nbytes
     out["d2h"] = com_h.nbytes + hoek_h.nbytes + nch * 128
@@ -247,7 +250,7 @@ def measure_leg(eng, system, box, nch, S, steps, warmup, seeds, stream, flush, b
         eng.set_state(com_h, hoek_h)          # pinned staging + cudaMemcpy2DAsync inside the library
         eng.run_steps(S, want_counts=False)   # includes the start-up recompute the new state requires
         st = eng.stats()
-        com_h, hoek_h = eng.get_state()
+        eng.get_state(out=(com_h, hoek_h))
         b.record(stream)
         barrier()
         if k > 0:
@@ -400,7 +403,7 @@ def run_gpu_arm(args):
             "oracle_check": {**m1["check"], "all_ranks_ok": ok1},
             "e2e": {"value": w_e2e_all / t_e2e_all, "unit": UNIT, "h2d_bytes_per_step": m1["h2d"], "d2h_bytes_per_step": m1["d2h"],
                     "ms_per_step": 1e3 * t_e2e_all / max(len(m1["e2e_ms"]), 1),
-                    "path": "mcb_set_chain_state -> mcb_run_steps -> mcb_get_stats + mcb_get_chain_state (host numpy buffers)"},
+                    "path": "mcb_set_chain_state -> mcb_run_steps -> mcb_get_stats + mcb_get_chain_state (page-locked host numpy buffers)"},
             "gpu_launches": int(m1["launches"]),
             "clocks": clocks,
             "roofline": roofline(m1, "k_run_spec", alg1, "k_run_spec"),

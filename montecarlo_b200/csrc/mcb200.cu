@@ -42,7 +42,8 @@ struct mcb_handle {
     // scratch for entry-point inputs/outputs
     int *d_rsolv = nullptr; double *d_vec = nullptr; double *d_out = nullptr; long long *d_ll = nullptr;
     unsigned char *d_acc = nullptr; double *d_ubuf = nullptr; size_t ubuf_cap = 0;
-    double *pin = nullptr; size_t pin_doubles = 0;   // pinned staging
+    double *pin = nullptr; size_t pin_doubles = 0;   // pinned staging (solute tables)
+    double *d_stage = nullptr; size_t stage_doubles = 0;   // device staging of the caller's AoS coordinate arrays
     std::vector<double> site_tab;                     // [4][3] padded
     std::vector<double> tab0AB, tab0Q;                // type-0 tables
     long long launches = 0;
@@ -144,7 +145,7 @@ extern "C" int mcb_destroy(mcb_t *h)
     comm_free(h);
     cudaFree(h->images); cudaFree(h->matg); cudaFree(h->work); cudaFree(h->ctl);
     cudaFree(h->d_rsolv); cudaFree(h->d_vec); cudaFree(h->d_out); cudaFree(h->d_ll); cudaFree(h->d_acc);
-    cudaFree(h->d_ubuf);
+    cudaFree(h->d_ubuf); cudaFree(h->d_stage);
     cudaFree(h->vl.idx); cudaFree(h->vl.cnt); cudaFree(h->vl.ref);
     cudaFree(h->big_e); cudaFree(h->big_sol); cudaFree(h->big_out); cudaFree(h->big_n); cudaFree(h->big_nout);
     cudaFree(h->cells.count); cudaFree(h->cells.cell_of); cudaFree(h->cells.order);
@@ -275,6 +276,10 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
         s.rng_key = x; s.rng_n = 0;
     }
     CKC(cudaMemcpy(h->ctl, ctl.data(), nc * sizeof(ChainCtl), cudaMemcpyHostToDevice));
+    if (!h->energy_only) {
+        const size_t pb = ((size_t)PREP_W * prepare_warp_doubles(g) + 3 * PREP_W) * 8;
+        if (set_smem_attr(h, k_prepare<true>, pb) || set_smem_attr(h, k_prepare<false>, pb)) return fail(-1);
+    }
     if (h->can_step) {
         int rc = 0;
         rc |= set_smem_attr(h, k_run_steps<false, false>, h->smem_bytes); rc |= set_smem_attr(h, k_run_steps<false, true>, h->smem_bytes);
@@ -348,6 +353,17 @@ extern "C" int mcb_set_solute(mcb_t *h, int chain0, int nchains, const double *s
     return 0;
 }
 
+// device staging for mcb_set_chain_state / mcb_get_chain_state: the caller's AoS arrays travel as they are (one
+// contiguous copy each) and a kernel moves them into / out of the images' SoA planes
+static int ensure_stage(mcb_t *h, size_t doubles)
+{
+    if (doubles <= h->stage_doubles) return 0;
+    cudaFree(h->d_stage); h->d_stage = nullptr; h->stage_doubles = 0;
+    CK(h, cudaMalloc(&h->d_stage, doubles * sizeof(double)));
+    h->stage_doubles = doubles;
+    return 0;
+}
+
 extern "C" int mcb_set_chain_state(mcb_t *h, int chain0, int nchains, const double *com, const double *hoek, int broadcast)
 {
     if (int rc = check_range(h, chain0, nchains)) return rc;
@@ -355,17 +371,13 @@ extern "C" int mcb_set_chain_state(mcb_t *h, int chain0, int nchains, const doub
     h->vl.trust = 0;   // new coordinates: the neighbour lists of k_run_vl are rebuilt at the next launch
     const Geo &g = h->g;
     CK(h, cudaSetDevice(h->device));
-    const int w = 6 * g.Np;   // com planes + hoek planes are adjacent at the head of the image
-    for (int c = 0; c < nchains; ++c) {
-        double *t = h->pin + (size_t)c * w;
-        const double *cc = com + (broadcast ? 0 : (size_t)c * g.N * 3), *hh = hoek + (broadcast ? 0 : (size_t)c * g.N * 3);
-        if (broadcast && c > 0) { memcpy(t, h->pin, sizeof(double) * w); continue; }
-        memset(t, 0, sizeof(double) * w);
-        for (int j = 0; j < g.N; ++j)
-            for (int k = 0; k < 3; ++k) { t[k * g.Np + j] = cc[3 * j + k]; t[(3 + k) * g.Np + j] = hh[3 * j + k]; }
-    }
-    CK(h, cudaMemcpy2DAsync(h->images + (size_t)chain0 * g.image_doubles, (size_t)g.image_doubles * 8, h->pin, (size_t)w * 8,
-                            (size_t)w * 8, nchains, cudaMemcpyHostToDevice, h->stream));
+    const size_t per = (size_t)g.N * 3, n = broadcast ? per : per * nchains;
+    if (int rc = ensure_stage(h, 2 * n)) return rc;
+    CK(h, cudaMemcpyAsync(h->d_stage, com, n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CK(h, cudaMemcpyAsync(h->d_stage + n, hoek, n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    k_state_pack<<<nchains, 128, 0, h->stream>>>(g, h->images, chain0, h->d_stage, h->d_stage + n, broadcast ? 1 : 0);
+    h->launches++;
+    CK(h, cudaGetLastError());
     CK(h, cudaStreamSynchronize(h->stream));
     h->dirty = true;
     return 0;
@@ -376,26 +388,23 @@ extern "C" int mcb_get_chain_state(mcb_t *h, int chain0, int nchains, double *co
     if (int rc = check_range(h, chain0, nchains)) return rc;
     const Geo &g = h->g;
     CK(h, cudaSetDevice(h->device));
-    const int w = 6 * g.Np;
-    CK(h, cudaMemcpy2DAsync(h->pin, (size_t)w * 8, h->images + (size_t)chain0 * g.image_doubles, (size_t)g.image_doubles * 8,
-                            (size_t)w * 8, nchains, cudaMemcpyDeviceToHost, h->stream));
+    const size_t n = (size_t)g.N * 3 * nchains;
+    if (int rc = ensure_stage(h, 2 * n)) return rc;
+    k_state_unpack<<<nchains, 128, 0, h->stream>>>(g, h->images, chain0, com ? h->d_stage : nullptr, hoek ? h->d_stage + n : nullptr);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    if (com) CK(h, cudaMemcpyAsync(com, h->d_stage, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (hoek) CK(h, cudaMemcpyAsync(hoek, h->d_stage + n, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     CK(h, cudaStreamSynchronize(h->stream));
-    for (int c = 0; c < nchains; ++c) {
-        const double *t = h->pin + (size_t)c * w;
-        for (int j = 0; j < g.N; ++j)
-            for (int k = 0; k < 3; ++k) {
-                if (com) com[((size_t)c * g.N + j) * 3 + k] = t[k * g.Np + j];
-                if (hoek) hoek[((size_t)c * g.N + j) * 3 + k] = t[(3 + k) * g.Np + j];
-            }
-    }
     return 0;
 }
 
 // ------------------------------------------------------------------------------------------------ energies
 static int launch_prepare(mcb_t *h, int chain0, int nchains, double *d_tot, double *d_esol, long long *d_pairs)
 {
-    if (h->coul) k_prepare<true><<<nchains, 32, 0, h->stream>>>(h->g, h->rel, h->images, h->matg, h->work, h->ctl, chain0, d_tot, d_esol, d_pairs);
-    else k_prepare<false><<<nchains, 32, 0, h->stream>>>(h->g, h->rel, h->images, h->matg, h->work, h->ctl, chain0, d_tot, d_esol, d_pairs);
+    const size_t bytes = ((size_t)PREP_W * prepare_warp_doubles(h->g) + 3 * PREP_W) * 8;
+    if (h->coul) k_prepare<true><<<nchains, 32 * PREP_W, bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, chain0, d_tot, d_esol, d_pairs);
+    else k_prepare<false><<<nchains, 32 * PREP_W, bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, chain0, d_tot, d_esol, d_pairs);
     h->launches++;
     CK(h, cudaGetLastError());
     return 0;

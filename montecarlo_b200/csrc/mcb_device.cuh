@@ -80,6 +80,23 @@ __device__ __forceinline__ double warp_sum(double v)
     return v;
 }
 
+// The same sum over the 32 lanes through the fp64 tensor-core product (mma.sync m8n8k4, DMMA): with an all-ones B,
+// D[i][j] = sum_k A[i][k] leaves in every lane the sum over its group of four lanes; lane (i, k) then fetches the
+// sums of groups k and k + 4 and a second product adds those four numbers.  Two DMMAs, two shuffled doubles and one
+// add instead of five shuffle-add levels; fixed (hardware) summation order, so deterministic like warp_sum.
+__device__ __forceinline__ double warp_sum_mma(double v, int lane)
+{
+    double g0, g1 = 0.0, t0, t1 = 0.0;
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%4,%5};"
+        : "=d"(g0), "=d"(g1) : "d"(v), "d"(1.0), "d"(0.0), "d"(0.0));
+    const int k = lane & 3;
+    const double u = shfl_d(g0, 4 * k) + shfl_d(g0, 4 * k + 16);
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%4,%5};"
+        : "=d"(t0), "=d"(t1) : "d"(u), "d"(1.0), "d"(0.0), "d"(0.0));
+    (void)g1; (void)t1;   // (every column of D holds the same sum)
+    return t0;
+}
+
 // Minimum image as the reference writes it, R - BOXL2*AINT(R/BOXL) with BOXL = half side
 // (LennardJones.f90:178-180) — not a nearest image once |R| >= 2*BOXL, and that is part of the contract.
 // Only the SQUARE of the result is ever used, so the kernel works on |R|:

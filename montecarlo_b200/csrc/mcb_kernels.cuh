@@ -22,19 +22,28 @@ constexpr double INV_SQRT3 = 0x1.279a74590331dp-1;              // 1.D0/sqrt(3.D
 // ---------------------------------------------------------------------------------------------------------
 // Start-up recompute.  Each unordered pair is evaluated once, with the LARGER index as MOL1 — the value the
 // reference's double evaluation leaves in SS(i,j) and SS(j,i) (last writer wins, MonteCarlo.F90:358-360,819-820).
+constexpr int PREP_W = 8;   // warps per chain in k_prepare: rows of the matrix are dealt out to them
+
+__host__ __device__ inline int prepare_warp_doubles(const Geo &g) { return g.Np + ((g.Np + g.nsolp + 1) / 2 + 1 & ~1); }
+
 template <bool COUL>
-__global__ void __launch_bounds__(32) k_prepare(Geo g, SiteRel rel, double *images, double *matg, double *work,
-                                                ChainCtl *ctl, int chain0, double *out_tot, double *out_esol,
-                                                long long *out_pairs)
+__global__ void __launch_bounds__(32 * PREP_W) k_prepare(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl, int chain0,
+                                                         double *out_tot, double *out_esol, long long *out_pairs)
 {
-    const int lane = threadIdx.x;
+    extern __shared__ __align__(16) double smem[];   // per warp: newrow[Np] + list[Np + nsolp]; then PREP_W x 3 partial sums
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int c = chain0 + blockIdx.x;
     double *img = images + (size_t)c * g.image_doubles;
     double *mat = g.mat_in_image ? img + g.o_mat : matg + (size_t)c * g.N * g.MS;
-    ChainPtrs p = chain_ptrs(g, img, mat, work + (size_t)c * g.work_doubles);
     const int N = g.N, Np = g.Np;
+    double *const mine = smem + warp * prepare_warp_doubles(g);
+    double *const red = smem + PREP_W * prepare_warp_doubles(g);
+    ChainPtrs p;
+    p.com = img + g.o_com; p.hoek = img + g.o_hoek; p.energy = img + g.o_energy; p.sites = img + g.o_sites;
+    p.tabAB = img + g.o_tabAB; p.tabQ = img + g.o_tabQ; p.mat = mat;
+    p.newrow = mine; p.list = reinterpret_cast<int *>(mine + Np);
 
-    for (int j = lane; j < N; j += 32) {   // RotMatrix for every molecule, lib.f90:27-83
+    for (int j = tid; j < N; j += 32 * PREP_W) {   // RotMatrix for every molecule, lib.f90:27-83
         double s1, c1, s2, c2, s3, c3;
         sincos(p.hoek[j], &s1, &c1); sincos(p.hoek[Np + j], &s2, &c2); sincos(p.hoek[2 * Np + j], &s3, &c3);
         double cx = p.com[j], cy = p.com[Np + j], cz = p.com[2 * Np + j];
@@ -45,12 +54,13 @@ __global__ void __launch_bounds__(32) k_prepare(Geo g, SiteRel rel, double *imag
             p.sites[SITE_DOUBLES * j + 3 * a + 2] = oz;
         }
     }
-    __syncwarp();
+    __syncthreads();
 
+    // row i = molecule i as MOL1 against every j < i: each unordered pair once, the larger index as MOL1
     const int a = lane & 3;
     long long pairs = 0;
     double esum = 0.0;
-    for (int i = 0; i < N; ++i) {
+    for (int i = warp; i < N; i += PREP_W) {
         double sx = p.sites[SITE_DOUBLES * i + 3 * a], sy = p.sites[SITE_DOUBLES * i + 3 * a + 1],
                sz = p.sites[SITE_DOUBLES * i + 3 * a + 2];
         double e_sol;
@@ -65,18 +75,48 @@ __global__ void __launch_bounds__(32) k_prepare(Geo g, SiteRel rel, double *imag
         }
         __syncwarp();
     }
-    // calcEnergy (MonteCarlo.F90:988-1004); lane-parallel partial sums, fixed order => deterministic
+    __syncthreads();
+    // calcEnergy (MonteCarlo.F90:988-1004): thread-parallel partial sums combined in a fixed order => deterministic
     double acc = 0.0;
-    for (int i = 0; i < N; ++i)
+    for (int i = warp; i < N; i += PREP_W)
         for (int j = i + 1 + lane; j < N; j += 32) acc += mat[(size_t)i * g.MS + j];
-    for (int i = lane; i < N; i += 32) acc += p.energy[i];
-    double tot = warp_sum(acc);
-    if (lane == 0) {
+    for (int i = tid; i < N; i += 32 * PREP_W) acc += p.energy[i];
+    acc = warp_sum(acc);
+    if (lane == 0) { red[3 * warp] = acc; red[3 * warp + 1] = esum; red[3 * warp + 2] = (double)pairs; }
+    __syncthreads();
+    if (tid == 0) {
+        double tot = 0.0, es = 0.0, np = 0.0;
+        for (int w = 0; w < PREP_W; ++w) { tot += red[3 * w]; es += red[3 * w + 1]; np += red[3 * w + 2]; }
         ctl[c].toteng = tot;
         ctl[c].energies_valid = 1;
         if (out_tot) out_tot[c - chain0] = tot;
-        if (out_esol) out_esol[c - chain0] = esum;
-        if (out_pairs) out_pairs[c - chain0] = pairs;
+        if (out_esol) out_esol[c - chain0] = es;
+        if (out_pairs) out_pairs[c - chain0] = (long long)np;
+    }
+}
+
+// AoS <-> SoA: the driver's TYPE(vector) arrays double[chain][molecule][3] and the images' planes x|y|z (a11)
+__global__ void __launch_bounds__(128) k_state_pack(Geo g, double *images, int chain0, const double *com, const double *hoek, int broadcast)
+{
+    const int c = chain0 + blockIdx.x;
+    double *img = images + (size_t)c * g.image_doubles;
+    const size_t src = broadcast ? 0 : (size_t)blockIdx.x * g.N * 3;
+    for (int q = threadIdx.x; q < 3 * g.Np; q += blockDim.x) {
+        const int k = q / g.Np, j = q - k * g.Np;
+        img[g.o_com + q] = j < g.N ? com[src + 3 * (size_t)j + k] : 0.0;
+        img[g.o_hoek + q] = j < g.N ? hoek[src + 3 * (size_t)j + k] : 0.0;
+    }
+}
+
+__global__ void __launch_bounds__(128) k_state_unpack(Geo g, const double *images, int chain0, double *com, double *hoek)
+{
+    const int c = chain0 + blockIdx.x;
+    const double *img = images + (size_t)c * g.image_doubles;
+    const size_t dst = (size_t)blockIdx.x * g.N * 3;
+    for (int q = threadIdx.x; q < 3 * g.N; q += blockDim.x) {
+        const int j = q / 3, k = q - 3 * j;
+        if (com) com[dst + q] = img[g.o_com + k * g.Np + j];
+        if (hoek) hoek[dst + q] = img[g.o_hoek + k * g.Np + j];
     }
 }
 
@@ -750,8 +790,11 @@ __global__ void __launch_bounds__(32 * W, W == 1 ? 1 : 7) k_run_spec(Geo g, Site
             c_rs_in = tot[c_j] + (c_e - mat[(size_t)i * MS + c_j]);
             c_rs_left = tot[r < N ? r : 0] - oldrow[0];
         }
+        if (GL == 32) dE = warp_sum_mma(dE, lane);   // (two DMMAs + two shuffled doubles instead of five shuffle-add levels: +3 %)
+        else {
 #pragma unroll
-        for (int o = GL / 2; o >= 1; o >>= 1) dE += shfl_xor_d(dE, o);
+            for (int o = GL / 2; o >= 1; o >>= 1) dE += shfl_xor_d(dE, o);
+        }
         // METROPOLIS (:720-788) on DELTA = dE
         const double exponent = dE * neg_inv_rt;
         const bool clamped = !(dE <= DBL_HUGE);                      // +Inf/NaN trial energy: clamped, rejected (:421-428); -Inf passes, as there

@@ -97,9 +97,16 @@ class LJEngine:
             assert com.shape[0] == nchains
         self._ck(self.lib.mcb_set_chain_state(self.h, chain0, nchains, _d(com), _d(hoek), bc), "mcb_set_chain_state")
 
-    def get_state(self, chain0: int = 0, nchains: int | None = None):
+    def get_state(self, chain0: int = 0, nchains: int | None = None, out=None):
+        """CoM / HOEK of the chains as [chain][molecule][3].  `out=(com, hoek)` reuses the caller's arrays (a driver
+        that keeps them page-locked - cudaHostRegister, or torch's pin_memory - gets the copy at full PCIe speed)."""
         chain0, nchains = self._range(chain0, nchains)
-        com = np.empty((nchains, self.n_mol, 3)); hoek = np.empty((nchains, self.n_mol, 3))
+        if out is None:
+            com = np.empty((nchains, self.n_mol, 3)); hoek = np.empty((nchains, self.n_mol, 3))
+        else:
+            com, hoek = out
+            assert com.shape == hoek.shape == (nchains, self.n_mol, 3) and com.dtype == hoek.dtype == np.float64
+            assert com.flags.c_contiguous and hoek.flags.c_contiguous
         self._ck(self.lib.mcb_get_chain_state(self.h, chain0, nchains, _d(com), _d(hoek)), "mcb_get_chain_state")
         return com, hoek
 
