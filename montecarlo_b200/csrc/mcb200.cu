@@ -133,7 +133,9 @@ static void setup_geo(mcb_handle *h)
     h->smem_bytes = ((size_t)g.stage_doubles + g.work_doubles) * 8;
     // image + look-ahead work areas + exchange + ring (threshold, moves, picks) + tot[] + sin/cos cache + ring of sin/cos + moved bits
     h->smem_spec_bytes = ((size_t)g.stage_doubles + (size_t)h->lookahead * (g.work_doubles + SPECX_DOUBLES) + 64 + 6 * 64 + 32 + g.Np + 6 * g.Np + 6 * 64 + (g.N + 63) / 64 + 2) * 8;
-    h->can_step = h->smem_spec_bytes <= 227 * 1024;
+    // a box whose matrix lives in global memory steps with the neighbour-list kernels, which need less shared memory
+    // than k_run_spec's plan (no sin/cos cache); k_run_spec is then only the list-free fall-back and may not fit
+    h->can_step = (g.mat_in_image ? h->smem_spec_bytes : (size_t)vl_smem_doubles(g) * 8) <= 227 * 1024;
 }
 
 extern "C" const char *mcb_last_error(const mcb_t *h) { return h ? h->err.c_str() : g_create_err.c_str(); }
@@ -287,10 +289,12 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
 #define SPEC_ATTR1(GL, W, S) rc |= set_smem_attr(h, k_run_spec<false, false, GL, W, S>, h->smem_spec_bytes); rc |= set_smem_attr(h, k_run_spec<false, true, GL, W, S>, h->smem_spec_bytes); \
                             rc |= set_smem_attr(h, k_run_spec<true, false, GL, W, S>, h->smem_spec_bytes);  rc |= set_smem_attr(h, k_run_spec<true, true, GL, W, S>, h->smem_spec_bytes);
 #define SPEC_ATTR(GL, W) SPEC_ATTR1(GL, W, true) SPEC_ATTR1(GL, W, false)
+        if (h->smem_spec_bytes <= 227 * 1024) {
         SPEC_ATTR(32, 1)
 #ifndef MCB_DEV_BUILD   // (-DMCB_DEV_BUILD: only the default variant, for a quick compile while tuning)
         SPEC_ATTR(16, 1) SPEC_ATTR(8, 1) SPEC_ATTR(16, 2) SPEC_ATTR(8, 2) SPEC_ATTR(32, 2) SPEC_ATTR(32, 4)
 #endif
+        }
 #undef SPEC_ATTR
 #undef SPEC_ATTR1
         if (rc) return fail(rc);
@@ -831,11 +835,13 @@ extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, i
             }
             h->vl.trust = 1;
         } else if (h->vl.idx) {
-            set_smem_attr(h, k_run_vl<true>, h->smem_spec_bytes); set_smem_attr(h, k_run_vl<false>, h->smem_spec_bytes);
-            if (h->coul) k_run_vl<true><<<h->n_chains, 32, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);
-            else k_run_vl<false><<<h->n_chains, 32, h->smem_spec_bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);
+            const size_t vb = (size_t)vl_smem_doubles(h->g) * 8;   // (its own size: k_run_spec's plan has grown caches this kernel does not use)
+            set_smem_attr(h, k_run_vl<true>, vb); set_smem_attr(h, k_run_vl<false>, vb);
+            if (h->coul) k_run_vl<true><<<h->n_chains, 32, vb, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);
+            else k_run_vl<false><<<h->n_chains, 32, vb, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);
             h->vl.trust = 1;   // until an entry point other than this one changes the coordinates
-        } else if (h->coul) launch_run_spec_any<true>(h, nsteps, d_steps); else launch_run_spec_any<false>(h, nsteps, d_steps);
+        } else if (h->smem_spec_bytes > 227 * 1024) return arg_err(h, "mcb_run_steps: without neighbour lists a chain of this size does not fit in shared memory");
+        else if (h->coul) launch_run_spec_any<true>(h, nsteps, d_steps); else launch_run_spec_any<false>(h, nsteps, d_steps);
     }
     h->launches++;
     CK(h, cudaGetLastError());

@@ -23,6 +23,9 @@ constexpr int VL_K = 64;   // list capacity per molecule (two 32-lane chunks); c
 // trust: nothing but k_run_vl has changed the coordinates since the last launch, so valid lists are kept across launches
 struct VerletBufs { unsigned short *idx; int *cnt; double *ref; double skin; int trust; };
 
+// shared memory of k_run_vl: image, one work area, exchange record, ring (threshold, moves, picks), row sums
+__host__ __device__ inline int vl_smem_doubles(const Geo &g) { return g.stage_doubles + g.work_doubles + SPECX_DOUBLES + 64 + 6 * 64 + 32 + g.Np + 2; }
+
 template <bool COUL>
 __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl,
                                                long long nsteps, long long *out_steps, VerletBufs vb)
@@ -236,8 +239,7 @@ __global__ void __launch_bounds__(32) k_run_vl(Geo g, SiteRel rel, double *image
 #pragma unroll 1
             for (int p = sub + 8; p < nsolp; p += 8) esol += epart[4 * p + a];
         }
-#pragma unroll
-        for (int o = 16; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
+        dE = warp_sum_mma(dE, lane); esol = warp_sum_mma(esol, lane);   // (fp64 tensor-core sums, as k_run_spec)
         // ---- METROPOLIS (:720-788) on DELTA = dE
         const double exponent = dE * neg_inv_rt;
         const bool clamped = !(dE <= DBL_HUGE);   // -Inf is not clamped (MonteCarlo.F90:421-428)

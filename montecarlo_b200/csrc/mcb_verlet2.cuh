@@ -331,8 +331,7 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
 #pragma unroll 1
                 for (int p2 = sub + 8; p2 < nsolp; p2 += 8) esol += ep[4 * p2 + a];
             }
-#pragma unroll
-            for (int o = 16; o >= 1; o >>= 1) { dE += shfl_xor_d(dE, o); esol += shfl_xor_d(esol, o); }
+            dE = warp_sum_mma(dE, lane); esol = warp_sum_mma(esol, lane);   // (fp64 tensor-core sums, as k_run_spec)
             // ---- METROPOLIS (:720-788) on DELTA = dE
             const double exponent = dE * neg_inv_rt;
             clamped = !(dE <= DBL_HUGE);   // -Inf is not clamped (MonteCarlo.F90:421-428)
