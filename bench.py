@@ -370,10 +370,18 @@ def run_gpu_arm(args):
             t_launch = m["t"] / max(m["launches"], 1)
             achieved_tf = w_launch * FLOP_PER_SITEPAIR / t_launch / 1e12
             tr = traffic.get(tkey, {})
+            moves_launch = m["moves"] / max(m["launches"], 1)
+            dram_move, l2_move, dram_launch = tr.get("dram_bytes_per_move"), tr.get("l2_bytes_per_move"), tr.get("dram_bytes_per_launch")
+            if tr.get("scales_with") == "launch":      # the capture's bytes belong to a launch (image in, image out), whatever its length
+                dram_move = dram_launch / moves_launch
+                l2_move = tr.get("l2_bytes_per_launch", 0.0) / moves_launch
+            elif tr.get("scales_with") == "move" and dram_move is not None:
+                dram_launch = dram_move * moves_launch
             return {"bound": "fp64", "achieved": achieved_tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / peak_tf,
-                    "traffic": tr.get("dram_bytes_per_launch"), "kernel": kernel, "flop_per_site_pair": FLOP_PER_SITEPAIR,
+                    "traffic": dram_launch, "kernel": kernel, "flop_per_site_pair": FLOP_PER_SITEPAIR,
                     "site_pairs_per_launch": w_launch, "kernel_ms": 1e3 * t_launch,
-                    "dram_bytes_per_move": tr.get("dram_bytes_per_move"), "l2_bytes_per_move": tr.get("l2_bytes_per_move"),
+                    "dram_bytes_per_move": dram_move, "l2_bytes_per_move": l2_move,
+                    "warp_instructions_per_move": tr.get("warp_instructions_per_move"),
                     "traffic_source": tr.get("source"),
                     "peak_source": "measured live: mcb_measure_fp64_peak (independent DFMA chains, all SMs, loop-invariant "
                                    "multiplier and addend: 98 % of the nominal 148 SM x 64 DFMA/clk x 1.965 GHz); "

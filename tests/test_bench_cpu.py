@@ -1,6 +1,6 @@
 """bench.py's contract, as far as it can be checked without a GPU: the reference arm prints exactly one JSON line on
-stdout with the keys the driver reads, and the committed round result (profiles/bench_r01.json) carries the
-roofline, CPU-baseline and end-to-end objects."""
+stdout with the keys the driver reads, and the committed round result (profiles/bench_r02.json) carries the
+roofline, CPU-baseline and end-to-end objects, for the headline workload and for the target box."""
 import json
 import subprocess
 import sys
@@ -31,7 +31,7 @@ def test_reference_arm_prints_one_json_line():
 
 
 def test_committed_round_result_has_the_contract_keys():
-    d = json.loads((ROOT / "profiles" / "bench_r01.json").read_text())
+    d = json.loads((ROOT / "profiles" / "bench_r02.json").read_text())
     assert BASE_KEYS | {"gpu_launches", "clocks", "roofline", "cpu_baseline"} <= set(d)
     assert d["n_gpus"] == 1 and d["warmup"] >= 3 and d["gpu_launches"] >= d["steps"]
     rf = d["roofline"]
@@ -40,3 +40,11 @@ def test_committed_round_result_has_the_contract_keys():
     e = d["e2e"]
     assert e["h2d_bytes_per_step"] > 0 and e["d2h_bytes_per_step"] > 0 and 0 < e["value"] <= d["value"]
     assert not set(d["clocks"]["reasons"]) & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
+    assert d["oracle_check"]["ok"] and d["oracle_check"]["all_ranks_ok"]
+    # the box north_star's target is quoted on rides in the same line
+    t = d["target_box"]
+    assert "240 molecules" in t["workload"] and t["chains_per_gpu"] == 512 and t["oracle_check"]["ok"]
+    assert abs(t["roofline"]["frac"] - t["roofline"]["achieved"] / t["roofline"]["peak"]) < 1e-9
+    assert 0 < t["e2e"]["value"] <= t["value"] and t["gpu_launches"] >= d["steps"]
+    for r in (rf, t["roofline"]):
+        assert r["dram_bytes_per_move"] > 0 and r["l2_bytes_per_move"] > 0
