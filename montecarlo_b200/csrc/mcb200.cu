@@ -99,7 +99,7 @@ static void setup_geo(mcb_handle *h)
     g.MS = (g.N % 2) ? g.N : g.N + 1;
     g.o_com = 0; g.o_hoek = 3 * g.Np; g.o_energy = 6 * g.Np; g.o_sites = 7 * g.Np;
     g.o_tabAB = g.o_sites + SITE_DOUBLES * (g.N + g.nsolp);
-    g.o_tabQ = g.o_tabAB + (1 + g.nsolp) * 32;
+    g.o_tabQ = g.o_tabAB + (1 + g.nsolp) * 4 * TAB_ROW;
     int end_tab = g.o_tabQ + (1 + g.nsolp) * 16;
     g.o_mat = end_tab;
     g.o_newrow = 0; g.o_list = g.Np;
@@ -195,12 +195,12 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
     for (int a = 0; a < p->n_sites; ++a)
         for (int k = 0; k < 3; ++k) { h->rel.r[3 * a + k] = p->site_rel[3 * a + k]; h->site_tab[3 * a + k] = p->site_tab[3 * a + k]; }
     for (int a = p->n_sites; a < 4; ++a) { h->rel.r[3 * a] = 1.0e4 + 7.0 * a; h->rel.r[3 * a + 1] = 2.0e4; h->rel.r[3 * a + 2] = 3.0e4; }
-    h->tab0AB.assign(32, 0.0); h->tab0Q.assign(16, 0.0);
+    h->tab0AB.assign(4 * TAB_ROW, 0.0); h->tab0Q.assign(16, 0.0);
     for (int a = 0; a < p->n_sites; ++a)
         for (int b = 0; b < p->n_sites; ++b) {
             double A, B, Q;
             pair_consts(&h->site_tab[3 * a], &h->site_tab[3 * b], p->conv, A, B, Q);
-            h->tab0AB[(a * 4 + b) * 2] = A; h->tab0AB[(a * 4 + b) * 2 + 1] = B; h->tab0Q[a * 4 + b] = Q;
+            h->tab0AB[a * TAB_ROW + 2 * b] = A; h->tab0AB[a * TAB_ROW + 2 * b + 1] = B; h->tab0Q[a * 4 + b] = Q;
         }
     const size_t nc = (size_t)h->n_chains;
     CKC(cudaMalloc(&h->images, nc * g.image_doubles * sizeof(double)));
@@ -331,7 +331,7 @@ extern "C" int mcb_set_solute(mcb_t *h, int chain0, int nchains, const double *s
         const double *xyz = solute ? solute + (broadcast ? 0 : (size_t)c * g.nsol * 3) : nullptr;
         const double *tb = sol_tab ? sol_tab + (broadcast ? 0 : (size_t)c * g.nsol * 3) : nullptr;
         memset(t, 0, sizeof(double) * tail);
-        memcpy(ab, h->tab0AB.data(), 32 * sizeof(double));
+        memcpy(ab, h->tab0AB.data(), 4 * TAB_ROW * sizeof(double));
         memcpy(tq, h->tab0Q.data(), 16 * sizeof(double));
         for (int p = 0; p < g.nsolp; ++p)
             for (int b = 0; b < 4; ++b) {
@@ -342,7 +342,7 @@ extern "C" int mcb_set_solute(mcb_t *h, int chain0, int nchains, const double *s
                     for (int a = 0; a < h->n_sites; ++a) {
                         double A, B, Q;
                         pair_consts(&h->site_tab[3 * a], tb + 3 * atom, h->prm.conv, A, B, Q);
-                        ab[(((1 + p) * 4 + a) * 4 + b) * 2] = A; ab[(((1 + p) * 4 + a) * 4 + b) * 2 + 1] = B;
+                        ab[((1 + p) * 4 + a) * TAB_ROW + 2 * b] = A; ab[((1 + p) * 4 + a) * TAB_ROW + 2 * b + 1] = B;
                         tq[((1 + p) * 4 + a) * 4 + b] = Q;
                     }
                 } else {   // padding atom: no parameters, parked far outside any box

@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(128) k_cell_pairs(Geo g, const double *img, Ce
                         for (int a = 0; a < NSITE; ++a)              // calcLJ: a outer over MOL1, bb inner over MOL2 (LennardJones.f90:65-79)
                             for (int bb = 0; bb < NSITE; ++bb)
                                 en = site_pair_acc<COUL>(en, s2[3 * bb] - s1[3 * a], s2[3 * bb + 1] - s1[3 * a + 1], s2[3 * bb + 2] - s1[3 * a + 2],
-                                                         tabAB[(a * 4 + bb) * 2], tabAB[(a * 4 + bb) * 2 + 1], COUL ? tabQ[a * 4 + bb] : 0.0, g);
+                                                         tabAB[a * TAB_ROW + 2 * bb], tabAB[a * TAB_ROW + 2 * bb + 1], COUL ? tabQ[a * 4 + bb] : 0.0, g);
                         e += en;
                     }
                 }

@@ -15,6 +15,10 @@ namespace mcb {
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int NSITE = 4;          // interacting sites per solvent molecule (lane & 3 owns one)
 constexpr int SITE_DOUBLES = 12;  // one molecule's rotated sites: [site][xyz]
+// One (type, own site a) row of tabAB: four (A, B) pairs + one pair of padding.  With 64-byte rows every row starts on
+// bank 0 or 16 and the 16 rows a quarter-warp reads at once collide 8 ways (ncu: 10 shared-memory wavefronts per load,
+// the largest single user of the shared-memory pipe); with 80-byte rows they spread over all 32 banks.
+constexpr int TAB_ROW = 10;
 
 // Per-chain "image": every array a chain's warp touches, contiguous in HBM so that staging it into shared
 // memory is one linear, coalesced copy.  Offsets are in doubles.
@@ -24,7 +28,7 @@ constexpr int SITE_DOUBLES = 12;  // one molecule's rotated sites: [site][xyz]
 //   sites  [N+nsolp][4][3]  rotated absolute site coordinates (cache of RotMatrix output, lib.f90:27-83);
 //                       entries N.. are the solute atoms grouped in fours ("pseudo-molecules"), padded with
 //                       far-away atoms whose parameters are zero
-//   tabAB  [1+nsolp][4][4][2]  (A,B) = (4 eps s^12, 4 eps s^6) for (type, own site a, other site b);
+//   tabAB  [1+nsolp][4][TAB_ROW]  (A,B) = (4 eps s^12, 4 eps s^6) for (type, own site a, other site b), rows padded;
 //                       type 0 = solvent-solvent, type 1+p = solute pseudo-molecule p
 //   tabQ   [1+nsolp][4][4]     q_a q_b conv (only read when conv != 0)
 //   mat    [N][MS]      pair matrix SOLVENTSOLVENT (MS odd: conflict-free column access in shared memory);
@@ -261,7 +265,7 @@ __device__ __forceinline__ int row_eval(const Geo &g, const ChainPtrs &p, int i,
             if (s < nn) { j = p.list[s]; vm = j; t = 0; }
             else { vm = g.N + (s - nn); t = 1 + (s - nn); }
             const double2 *sp = reinterpret_cast<const double2 *>(p.sites + SITE_DOUBLES * vm);
-            const double2 *ab = reinterpret_cast<const double2 *>(p.tabAB) + (t * 4 + a) * 4;
+            const double2 *ab = reinterpret_cast<const double2 *>(p.tabAB) + (t * 4 + a) * (TAB_ROW / 2);
             double2 v0 = sp[0], v1 = sp[1], v2 = sp[2], v3 = sp[3], v4 = sp[4], v5 = sp[5];
             double2 p0 = ab[0], p1 = ab[1], p2 = ab[2], p3 = ab[3];
             double q0 = 0, q1 = 0, q2 = 0, q3 = 0;

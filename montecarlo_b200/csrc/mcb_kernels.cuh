@@ -217,7 +217,7 @@ __device__ __forceinline__ double item_energy(const Geo &g, const double *sites,
                                               int vm, int t, int a, double sx, double sy, double sz)
 {
     const double2 *sp = reinterpret_cast<const double2 *>(sites + SITE_DOUBLES * vm);
-    const double2 *ab = reinterpret_cast<const double2 *>(tabAB) + (t * 4 + a) * 4;
+    const double2 *ab = reinterpret_cast<const double2 *>(tabAB) + (t * 4 + a) * (TAB_ROW / 2);
     double2 v0 = sp[0], v1 = sp[1], v2 = sp[2], v3 = sp[3], v4 = sp[4], v5 = sp[5];
     double2 p0 = ab[0], p1 = ab[1], p2 = ab[2], p3 = ab[3];
     double q0 = 0, q1 = 0, q2 = 0, q3 = 0;
@@ -288,7 +288,7 @@ __device__ __forceinline__ double items_staged(const Geo &g, const double *sites
 #pragma unroll
     for (int n = 0; n < NI; ++n) {
         const int t = slot[n] < nsolp ? 1 + slot[n] : 0;
-        const double2 *ab = reinterpret_cast<const double2 *>(tabAB) + (t * 4 + a) * 4;
+        const double2 *ab = reinterpret_cast<const double2 *>(tabAB) + (t * 4 + a) * (TAB_ROW / 2);
         double en = 0.0;
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
@@ -1061,7 +1061,7 @@ __global__ void __launch_bounds__(128) k_big_pairs(Geo g, const double *img, int
             for (int a = 0; a < NSITE; ++a)          // calcLJ: a outer over MOL1, bb inner over MOL2 (LennardJones.f90:65-79)
                 for (int bb = 0; bb < NSITE; ++bb)
                     en = site_pair_acc<COUL>(en, s2[3 * bb] - s1[3 * a], s2[3 * bb + 1] - s1[3 * a + 1], s2[3 * bb + 2] - s1[3 * a + 2],
-                                             tabAB[(a * 4 + bb) * 2], tabAB[(a * 4 + bb) * 2 + 1], COUL ? tabQ[a * 4 + bb] : 0.0, g);
+                                             tabAB[a * TAB_ROW + 2 * bb], tabAB[a * TAB_ROW + 2 * bb + 1], COUL ? tabQ[a * 4 + bb] : 0.0, g);
             e += en;
         }
     }
@@ -1085,7 +1085,7 @@ __global__ void __launch_bounds__(128) k_big_solute(Geo g, double *img, double *
                 for (int bb = 0; bb < 4; ++bb) {
                     const int t = ((1 + p) * 4 + a) * 4 + bb;
                     e = site_pair_acc<COUL>(e, s2[3 * bb] - s1[3 * a], s2[3 * bb + 1] - s1[3 * a + 1], s2[3 * bb + 2] - s1[3 * a + 2],
-                                            tabAB[2 * t], tabAB[2 * t + 1], COUL ? tabQ[t] : 0.0, g);
+                                            tabAB[((1 + p) * 4 + a) * TAB_ROW + 2 * bb], tabAB[((1 + p) * 4 + a) * TAB_ROW + 2 * bb + 1], COUL ? tabQ[t] : 0.0, g);
                 }
             }
         img[g.o_energy + i] = e;
