@@ -95,7 +95,12 @@ static void setup_geo(mcb_handle *h)
 {
     const mcb_params &p = h->prm;
     Geo &g = h->g;
-    g.N = p.n_mol; g.Np = (int)round_up(p.n_mol, 4); g.nsol = p.n_sol; g.nsolp = (p.n_sol + 3) / 4;
+    g.N = p.n_mol; g.nsol = p.n_sol; g.nsolp = (p.n_sol + 3) / 4;
+    // plane stride of the SoA coordinate arrays: even (16-byte alignment of what follows) and NOT a multiple of 16
+    // doubles - with a stride of 32 doubles (N = 30 rounded up) the six planes of one molecule, read by six lanes of
+    // one shared-memory load in MCINIT, all sit on the same bank
+    g.Np = (int)round_up(p.n_mol, 2);
+    if (g.Np % 16 == 0) g.Np += 2;
     g.MS = (g.N % 2) ? g.N : g.N + 1;
     g.o_com = 0; g.o_hoek = 3 * g.Np; g.o_energy = 6 * g.Np; g.o_sites = 7 * g.Np;
     g.o_tabAB = g.o_sites + SITE_DOUBLES * (g.N + g.nsolp);

@@ -22,7 +22,7 @@ constexpr int TAB_ROW = 10;
 
 // Per-chain "image": every array a chain's warp touches, contiguous in HBM so that staging it into shared
 // memory is one linear, coalesced copy.  Offsets are in doubles.
-//   com    [3][Np]      SoA planes x|y|z of the centres of mass          (reference CoM(:))
+//   com    [3][Np]      SoA planes x|y|z of the centres of mass          (reference CoM(:)); Np >= N even, not a multiple of 16
 //   hoek   [3][Np]      SoA planes of the Euler angles                   (reference HOEK(:))
 //   energy [Np]         solvent-solute energy per molecule               (reference ENERGY(:))
 //   sites  [N+nsolp][4][3]  rotated absolute site coordinates (cache of RotMatrix output, lib.f90:27-83);
