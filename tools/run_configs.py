@@ -62,7 +62,11 @@ def main():
     eng.set_mc_params(start_prod=args.steps // 2)
     eng.seed(partition.global_seeds(rank, world, n_total))
     e_start = eng.total_energy()[0]
+    # warm-up: three launches (they count as equilibration: the chains simply go on afterwards)
+    for _ in range(3):
+        eng.run_steps(args.launch, want_counts=False)
     torch.cuda.synchronize()
+    st_w = eng.stats()
     if world > 1:
         dist.barrier()
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -74,6 +78,21 @@ def main():
         left -= n
     t1.record(stream)
     torch.cuda.synchronize()
+    # one chain per rank at full size against the C restatement on the same stream (checker only, untimed)
+    sys.path.insert(0, str(ROOT / "tests"))
+    import oracle_lib as ol
+    st_c = eng.stats(0, 1)
+    osys = system if args.config == 3 else boxio.System(**{**system.__dict__, "solute": conf[mine[0]]})
+    o = ol.OracleChain(osys, b.com, b.hoek)
+    o.set_mc_params(start_prod=args.steps // 2)
+    o.total_energy()
+    o.run_steps_rng(3 * args.launch + args.steps, ol.rng_seed(start + 1), trace=False)
+    so = o.stats()
+    chain_ok = bool(st_c["nsuc"][0] == so["nsuc"] and st_c["sitepairs"][0] == so["sitepairs"]
+                    and abs(st_c["toteng"][0] - so["toteng"]) <= 1e-10 * abs(so["toteng"]))
+    okt = torch.tensor([1.0 if chain_ok else 0.0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
     ms = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -92,10 +111,15 @@ def main():
     mean_e = eng.gather_chains()["mean_e"]                                        # the one all-gather
     c1.record(stream); torch.cuda.synchronize()
     tot = {k: float(v[0]) for k, v in g.items()}
+    w_timed = torch.tensor([float((eng.stats()["sitepairs"] - st_w["sitepairs"]).sum()), float((eng.stats()["step"] - st_w["step"]).sum())],
+                           dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(w_timed, op=dist.ReduceOp.SUM)
     if rank == 0:
         sec = ms.item() * 1e-3
         line = {"config": args.config, "n_gpus": world, "n_molecules": b.n, "chains": n_total, "steps_per_chain": args.steps,
-                "seconds": sec, "site_pairs_per_s": tot["sitepairs"] / sec, "trial_moves_per_s": tot["step"] / sec,
+                "seconds": sec, "warmup_launches": 3, "site_pairs_per_s": w_timed[0].item() / sec, "trial_moves_per_s": w_timed[1].item() / sec,
+                "oracle_check_one_chain_per_rank": bool(okt.item() == 1.0),
                 "acceptance": tot["acceptance"], "mean_production_energy": tot["mean_e"], "start_energy_chain0": float(e_start[0]),
                 "collectives_ms": c0.elapsed_time(c1)}
         if args.config == 4:
