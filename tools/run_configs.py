@@ -103,6 +103,7 @@ def main():
             idt.copy_(torch.frombuffer(bytearray(comm_unique_id()), dtype=torch.uint8))
         dist.broadcast(idt, 0)
         eng.comm_init(world, rank, idt.cpu().numpy().tobytes(), n_total)
+    eng.reduce_stats()   # (a new communicator sets up its connections in its first collective: untimed)
     c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     c0.record(stream)
