@@ -27,6 +27,16 @@ b2 = boxio.replicate(box, 2)
 s2 = boxio.System(**{**system.__dict__, "boxl": b2.boxl, "solute": b2.solute})
 eng = LJEngine(s2, b2.n, n_chains=2)
 eng.set_state(b2.com, b2.hoek); eng.run_steps(30); print("N=240", eng.stats()["toteng"]); eng.close()
+# round-2 entry points: temperature ladder + exchange, end-of-run sums and gather (one rank), the one-warp list kernel
+eng = LJEngine(system, box.n, n_chains=6)
+eng.set_state(box.com, box.hoek); eng.set_mc_params(temperature=np.linspace(250.0, 500.0, 6)); eng.run_steps(40)
+print("exchange", eng.exchange([0, 2, 4], [1, 3, 5]), eng.exchange([1, 3], [2, 4], np.array([0.3, 0.9])))
+print("reduce", eng.reduce_stats()["nsuc"], eng.reduce_stats(4)["n_chains"], "gather", eng.gather_chains()["acceptance"][:2]); eng.reset_stats(); eng.close()
+import os
+os.environ["MCB200_NO_VL2"] = "1"
+eng = LJEngine(s2, b2.n, n_chains=2)
+eng.set_state(b2.com, b2.hoek); eng.run_steps(30); print("N=240, one-warp list kernel", eng.stats()["toteng"]); eng.close()
+del os.environ["MCB200_NO_VL2"]
 b5 = boxio.replicate(box, 5)
 s5 = boxio.System(**{**system.__dict__, "boxl": b5.boxl, "solute": b5.solute})
 eng = LJEngine(s5, b5.n, n_chains=1)
