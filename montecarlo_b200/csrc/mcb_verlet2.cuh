@@ -22,7 +22,8 @@
 
 namespace mcb {
 
-struct Vl2X { double dE; int flags, nn; };   // flags: 1 accept, 2 used8, 4 clamped, 8 far, 16 evaluated; bits 8..15: depends on earlier step j of the batch
+struct Vl2X { double dE; int flags, nn; };   // flags: 1 accept, 2 used8, 4 clamped, 8 far, 16 evaluated
+struct Vl2T { double ncx, ncy, ncz; int i, pad; };   // a step's molecule and trial centre of mass, for the dependency tests
 constexpr int VL2_MAX_W = 8;
 
 __host__ __device__ inline int vl2_small_slots(const Geo &g) { return VL_K + g.nsolp; }
@@ -30,7 +31,7 @@ __host__ __device__ inline int vl2_list_doubles(int slots) { return (((slots + 1
 __host__ __device__ inline int vl2_smem_doubles(const Geo &g, int w)
 {
     const int small = vl2_small_slots(g);
-    return g.stage_doubles + w * (vl2_list_doubles(small) + 4 * small) + 64 + 6 * 64 + 32 + 2 * VL2_MAX_W;
+    return g.stage_doubles + w * (vl2_list_doubles(small) + 4 * small) + 64 + 6 * 64 + 32 + 2 * VL2_MAX_W + 4 * VL2_MAX_W;
 }
 
 template <bool COUL, int W>
@@ -68,7 +69,8 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
     double *const ring_thr = p; p += 64;
     double *const ring_rv = p; p += 6 * 64;
     int *const ring_i = reinterpret_cast<int *>(p); p += 32;
-    Vl2X *const xch = reinterpret_cast<Vl2X *>(p);
+    Vl2X *const xch = reinterpret_cast<Vl2X *>(p); p += 2 * VL2_MAX_W;
+    Vl2T *const tpos = reinterpret_cast<Vl2T *>(p);
     unsigned short *const vidx = vb.idx + (size_t)c * N * VL_K;
     int *const vcnt = vb.cnt + (size_t)c * (N + 2);
     double *const vref = vb.ref + (size_t)c * 3 * Np;
@@ -134,6 +136,10 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
     int p_cnt = -1, p_idx[2] = {0, 0}, p_step = -1;
     double p_rfx = 0.0, p_rfy = 0.0, p_rfz = 0.0;
 
+    // the ordered pair (ga < gb) of steps whose dependency this lane tests after the exchange: pair index = lane / 4
+    int dp_gb = 1;
+    while (dp_gb * (dp_gb + 1) / 2 <= (lane >> 2)) ++dp_gb;
+    const int dp_ga = (lane >> 2) - dp_gb * (dp_gb - 1) / 2;
     Vl2X pend[W];
     int pend_n = 0, pend_done = 0;
     auto sum_stats = [&]() {   // TOTENG, production and energy sums of the steps committed by the previous batch, in step order
@@ -239,27 +245,6 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
         const bool use_list = cnt >= 0 && !far;
         // warp 0 can always evaluate (its work area holds a full scan); warp 1 only from its list
         const bool evaluate = active && (warp == 0 || use_list);
-        // ---- warps 1..: would the move of an earlier step j of this batch, if accepted, change anything this step looks
-        //      at?  Four lanes per earlier step, one distance test each; step j's trial centre of mass comes from the ring
-        //      and the committed coordinates (the same expression warp j evaluates).
-        int depmask = 0;
-        if (warp > 0) {
-            const int j = min(lane >> 2, warp - 1), t = lane & 3;
-            const int ej = (ring0 + done + j) & 63, ij = ring_i[ej];
-            const double ox = com[ij], oy = com[Np + ij], oz = com[2 * Np + ij];           // step j's molecule, committed
-            const double n0x = wrap_fma(ox + s.dposmax * ring_rv[6 * ej + 0], g.boxl2, g.boxl, g.inv_boxl);
-            const double n0y = wrap_fma(oy + s.dposmax * ring_rv[6 * ej + 1], g.boxl2, g.boxl, g.inv_boxl);
-            const double n0z = wrap_fma(oz + s.dposmax * ring_rv[6 * ej + 2], g.boxl2, g.boxl, g.inv_boxl);   // ... and at its trial position
-            const double bx = com[i], by = com[Np + i], bz = com[2 * Np + i];              // this step's molecule, committed
-            double tx = ox - ncx, ty = oy - ncy, tz = oz - ncz;                            // t = 0: was a partner of the trial position
-            if (t == 1) { tx = n0x - ncx; ty = n0y - ncy; tz = n0z - ncz; }                // t = 1: would become one
-            if (t == 2) { tx = ox - bx; ty = oy - by; tz = oz - bz; }                      // t = 2: entry of the old row, as committed
-            if (t == 3) { tx = n0x - bx; ty = n0y - by; tz = n0z - bz; }                   // t = 3: that entry after the move
-            const bool hit = (lane >> 2) < warp && (ij == i || !(pair_r2(tx, ty, tz, g) > g.cut2));
-            const unsigned hb = __ballot_sync(FULL, hit);
-#pragma unroll
-            for (int q = 0; q < W - 1; ++q) depmask |= ((hb >> (4 * q)) & 0xFu) ? (1 << q) : 0;
-        }
         // ---- centre-of-mass gate (:804-813) on the candidates, or on everybody (warp 0 only)
         int nn = 0;
         bool cin[2] = {false, false};
@@ -341,22 +326,46 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
         if (lane == 0) {
             Vl2X x;
             x.dE = dE; x.nn = nn;
-            x.flags = (accept ? 1 : 0) | (used8 ? 2 : 0) | (clamped ? 4 : 0) | (far ? 8 : 0) | (evaluate ? 16 : 0) | (depmask << 8);
+            x.flags = (accept ? 1 : 0) | (used8 ? 2 : 0) | (clamped ? 4 : 0) | (far ? 8 : 0) | (evaluate ? 16 : 0);
             xch[warp] = x;
+            Vl2T tp;
+            tp.ncx = ncx; tp.ncy = ncy; tp.ncz = ncz; tp.i = i; tp.pad = 0;
+            tpos[warp] = tp;
         }
         __syncthreads();
         Vl2X xs[W];
 #pragma unroll
         for (int q = 0; q < W; ++q) xs[q] = xch[q];
+        // ---- would the move of an earlier step ga of this batch, if accepted, change anything a later step gb looked at?
+        //      Every warp answers for all W(W-1)/2 ordered pairs at once, four lanes per pair, one distance test each, from
+        //      the trial positions the warps have just exchanged and the committed coordinates: the same molecule; molecule
+        //      i_ga inside the cutoff of gb's trial position before (t = 0) or after (t = 1) its own move; inside the cutoff
+        //      of gb's molecule as committed - an entry of gb's old row - before (t = 2) or after (t = 3).  (Round 1 had
+        //      each warp test its own step before the exchange, re-deriving the earlier trial positions: 17 % of the batch.)
+        bool hit = false;
+        if (dp_gb < W) {
+            const Vl2T A = tpos[dp_ga], B = tpos[dp_gb];
+            const double cax = com[A.i], cay = com[Np + A.i], caz = com[2 * Np + A.i];
+            const double cbx = com[B.i], cby = com[Np + B.i], cbz = com[2 * Np + B.i];
+            const int t = lane & 3;
+            const double px = (t & 1) ? A.ncx : cax, py = (t & 1) ? A.ncy : cay, pz = (t & 1) ? A.ncz : caz;   // step ga's molecule: committed / trial
+            const double qx = (t & 2) ? cbx : B.ncx, qy = (t & 2) ? cby : B.ncy, qz = (t & 2) ? cbz : B.ncz;   // step gb: trial position / its molecule as committed
+            hit = A.i == B.i || !(pair_r2(px - qx, py - qy, pz - qz, g) > g.cut2);
+        }
+        const unsigned hb = __ballot_sync(FULL, hit);
         // step k+q stands if it was evaluated, every step before it stands, and no ACCEPTED earlier step touched what it looked at
         int progress = 1;
         unsigned acc_valid = xs[0].flags & 1u;
 #pragma unroll
-        for (int q = 1; q < W; ++q)
-            if (progress == q && (xs[q].flags & 16) && (((unsigned)xs[q].flags >> 8) & acc_valid) == 0u) {
+        for (int q = 1; q < W; ++q) {
+            unsigned dm = 0u;   // bit a: step q depends on step a (pairs (a, q) sit at nibbles q(q-1)/2 + a of the ballot)
+#pragma unroll
+            for (int aa = 0; aa < q; ++aa) dm |= ((hb >> (4 * (q * (q - 1) / 2 + aa))) & 0xFu) ? (1u << aa) : 0u;
+            if (progress == q && (xs[q].flags & 16) && (dm & acc_valid) == 0u) {
                 progress = q + 1;
                 acc_valid |= (unsigned)(xs[q].flags & 1) << q;
             }
+        }
         const int nslots = nsolp + nn;
         // ---- commits, all at once: the standing accepted steps moved different molecules, none of which any other
         //      standing step looked at, so they write different matrix entries and different molecules' coordinates;
