@@ -5,9 +5,14 @@
     python bench.py --impl reference [--gpus N --steps K --warmup W]   the reference's own CPU code on the host cores
 
 A "step" is one pass of the hot path over one batch: `mcb_run_steps` advancing every chain on the GPU by
---mc-steps Metropolis steps (one kernel launch).  Workload = BASELINE.json configs[1]: the reference's shipped
+--mc-steps Metropolis steps (one kernel launch).  Headline workload = BASELINE.json configs[1]: the reference's shipped
 DMSO box (30 molecules + 11-atom solute), 1024 independent chains per GPU, T = 300 K, config0.ini step sizes.
-`value` = evaluated site-pair interactions per second (LJ_FORMULA evaluations of trial states), whole job.
+`value` = evaluated site-pair interactions per second (LJ_FORMULA evaluations of trial states), whole job; `e2e` = the
+same through the C ABI with page-locked host buffers, H2D and D2H copies inside the timed region.  A second timed leg,
+`target_box`, is the box north_star's target is quoted on: the 2x2x2 periodic replica (240 molecules), 512 chains per GPU
+= configs[2]'s per-GPU share (at --gpus 8 it is configs[2] at full size).  Each leg checks one chain per rank against the
+C restatement (untimed).  The job's one collective (statistics all-reduce + per-chain all-gather) runs inside
+libmcb200.so over NCCL.
 One JSON line on stdout (rank 0).
 """
 from __future__ import annotations

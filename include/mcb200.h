@@ -123,7 +123,8 @@ int mcb_row_energy(mcb_t *h, int chain, int i, double *ss_row, double *e_i);
 int mcb_trial_delta(mcb_t *h, int nchains, const int *rsolv, const double *new_com, const double *new_hoek,
                     double *d_e, double *e_new);
 /* replaces: the keep-or-roll-back at MonteCarlo.F90:779-786: accept[c] != 0 makes the pending trial of
- * chain c current; 0 discards it. */
+ * chain c current; 0 discards it.  Argument error when no trial is pending: mcb_set_chain_state and mcb_set_solute
+ * discard a parked trial (it was evaluated against a state that no longer exists). */
 int mcb_commit(mcb_t *h, int nchains, const unsigned char *accept);
 
 /* ---- batched mode: MCINIT + calculateLJ + calcEnergy + METROPOLIS looped on the GPU ----------------- */

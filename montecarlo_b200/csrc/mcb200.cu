@@ -325,6 +325,7 @@ extern "C" int mcb_set_solute(mcb_t *h, int chain0, int nchains, const double *s
 {
     if (int rc = check_range(h, chain0, nchains)) return rc;
     if ((solute == nullptr) != (sol_tab == nullptr)) return arg_err(h, "mcb_set_solute: solute and sol_tab must both be given");
+    h->trial_pending = false;
     const Geo &g = h->g;
     CK(h, cudaSetDevice(h->device));
     // the tail of an image: [solute pseudo-molecule sites][tabAB][tabQ], contiguous
@@ -378,6 +379,7 @@ extern "C" int mcb_set_chain_state(mcb_t *h, int chain0, int nchains, const doub
     if (int rc = check_range(h, chain0, nchains)) return rc;
     if (!com || !hoek) return arg_err(h, "mcb_set_chain_state: null array");
     h->vl.trust = 0;   // new coordinates: the neighbour lists of k_run_vl are rebuilt at the next launch
+    h->trial_pending = false;
     const Geo &g = h->g;
     CK(h, cudaSetDevice(h->device));
     const size_t per = (size_t)g.N * 3, n = broadcast ? per : per * nchains;
@@ -555,6 +557,9 @@ extern "C" int mcb_commit(mcb_t *h, int nchains, const unsigned char *accept)
     if (int rc = check_range(h, 0, nchains)) return rc;
     if (!accept) return arg_err(h, "mcb_commit: null array");
     if (h->energy_only) return arg_err(h, "mcb_commit: this handle is in energy-only mode");
+    // (new coordinates or a new solute since mcb_trial_delta drop the parked trial: committing it would apply a move
+    //  that was evaluated against a state that no longer exists)
+    if (!h->trial_pending) return arg_err(h, "mcb_commit: no trial is pending (call mcb_trial_delta first; mcb_set_chain_state / mcb_set_solute discard a pending trial)");
     h->vl.trust = 0;
     h->trial_pending = false;
     CK(h, cudaSetDevice(h->device));

@@ -854,6 +854,23 @@ def test_reset_stats_keeps_the_stream_position(shipped, k):
     assert np.array_equal(c_eq, c_again)
 
 
+def test_commit_needs_a_pending_trial(shipped):
+    """mcb_commit without a trial, or after new coordinates have replaced the state the trial was evaluated against, is an
+    argument error - not a silent commit of a stale move."""
+    box, system = shipped
+    from montecarlo_b200.engine import McbError
+    eng = _engine(system, box.n, n_chains=1)
+    eng.set_state(box.com, box.hoek)
+    e0 = eng.total_energy()[0][0]
+    with pytest.raises(McbError, match="no trial is pending"):
+        eng.commit([1])
+    eng.trial_delta([3], box.com[2] + 0.2, box.hoek[2])
+    eng.set_state(box.com, box.hoek)                 # discards the parked trial
+    with pytest.raises(McbError, match="no trial is pending"):
+        eng.commit([1])
+    assert eng.total_energy()[0][0] == e0 and np.array_equal(eng.get_state()[0][0], box.com)
+
+
 def test_row_energy_refuses_while_a_trial_is_pending(shipped):
     box, system = shipped
     from montecarlo_b200.engine import McbError
