@@ -937,3 +937,60 @@ def test_replica_exchange_ladder(shipped, stream):
     from montecarlo_b200.engine import McbError
     with pytest.raises(McbError, match="at most one pair"):
         eng.exchange([0, 1], [1, 2])
+
+
+def _lattice_box(n, boxl, rng, jitter=0.35):
+    """n molecules on a jittered cubic lattice inside (-boxl, boxl)^3 with random orientations: liquid-like distances
+    (no overlaps that would make every energy 1e10) at any n and box size."""
+    m = int(np.ceil(n ** (1.0 / 3.0)))
+    cells = np.stack(np.meshgrid(*[np.arange(m)] * 3, indexing="ij"), axis=-1).reshape(-1, 3)
+    pick = rng.permutation(len(cells))[:n]
+    com = (cells[pick] + 0.5) * (2.0 * boxl / m) - boxl + rng.uniform(-jitter, jitter, (n, 3))
+    return np.clip(com, -0.999 * boxl, 0.999 * boxl), rng.uniform(-np.pi, np.pi, (n, 3))
+
+
+SWEEP = [
+    # n, boxl, solute atoms, conv != 0, steps      what the case is for
+    (2, 6.0, 11, False, 600),      # two molecules: a single partner slot
+    (3, 8.0, 0, False, 600),       # no solute: no solute slots in the passes, ENERGY(:) = 0
+    (5, 7.0, 1, False, 600),       # one solute atom: one pseudo-molecule with three padding atoms
+    (17, 7.5, 11, False, 500),
+    (30, 5.2, 11, False, 500),     # box smaller than the cutoff sphere: nearly every molecule is a partner, every pass full
+    (31, 8.0, 5, True, 500),       # solute atoms not a multiple of four, Coulomb on
+    (32, 8.0, 11, False, 500),     # the last size whose matrix is staged with one 32-molecule chunk
+    (48, 9.0, 0, False, 400),      # global matrix, neighbour lists, no solute
+    (64, 10.0, 7, True, 400),
+    (100, 12.0, 11, False, 400),
+    (150, 9.0, 11, False, 300),    # dense: neighbour lists overflow their 64 entries -> the full scan takes over
+]
+
+
+@pytest.mark.parametrize("case", SWEEP, ids=[f"n{c[0]}_boxl{c[1]}_sol{c[2]}{'_coul' if c[3] else ''}" for c in SWEEP])
+def test_random_boxes_against_oracle(shipped, case):
+    """Sizes, densities and solutes the fixtures do not hold: start-up energy, then the default stepping path for a few
+    hundred steps with the built-in stream, decision for decision against the oracle, on two chains."""
+    box, system = shipped
+    n, boxl, nsol, coul, steps = case
+    rng = np.random.default_rng(1000 + n)
+    com, hoek = _lattice_box(n, boxl, rng)
+    s = boxio.System(**{**system.__dict__, "boxl": boxl, "solute": system.solute[:nsol].copy(), "sol_tab": system.sol_tab[:nsol].copy(),
+                        "conv": ol.lib().mco_const_conv_intended() if coul else system.conv, "sol_sym": list(system.sol_sym[:nsol])})
+    eng = _engine(s, n, n_chains=2, with_solute=nsol > 0)
+    eng.set_state(com, hoek)
+    eng.set_mc_params(nadj=37, start_prod=steps // 3)
+    seeds = np.array([11, 12], dtype=np.uint64)
+    eng.seed(seeds)
+    tot0 = eng.total_energy()[0]
+    eng.run_steps(steps // 2)
+    eng.run_steps(steps - steps // 2)
+    st = eng.stats()
+    c_, h_ = eng.get_state()
+    fresh = eng.total_energy()[0]
+    for c in range(2):
+        o = ol.OracleChain(s, com, hoek)
+        o.set_mc_params(nadj=37, start_prod=steps // 3)
+        e0 = o.total_energy()
+        assert abs(tot0[c] - e0) <= RTOL * abs(e0) + 1e-300
+        o.run_steps_rng(steps, ol.rng_seed(int(seeds[c])), trace=False)
+        _compare_chain(st, c, o.stats(), c_, h_, o)
+        assert abs(fresh[c] - st["toteng"][c]) <= RTOL * abs(fresh[c]) + 1e-300
