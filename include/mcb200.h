@@ -144,7 +144,11 @@ int mcb_seed_chains(mcb_t *h, int chain0, int nchains, const uint64_t *seeds);
  * plus 1 only when METROPOLIS draws (:739).  A chain stops early when fewer than 8 remain; consumed[c]
  * (may be NULL) receives how many it used, steps_done[c] (may be NULL) how many steps it made.  With
  * uniforms, consumed and steps_done all NULL the call only enqueues the kernel on the handle's stream and
- * returns; any later call that reads results (mcb_get_stats, mcb_get_chain_state, ...) waits for it. */
+ * returns; any later call that reads results (mcb_get_stats, mcb_get_chain_state, ...) waits for it.
+ * Box sizes: up to ~1400 molecules a chain's coordinates and site cache are staged in the SM's shared memory and both
+ * kinds of stream work; a larger box (up to 65535 molecules, as long as the pair matrices fit in the GPU's memory) steps
+ * with the built-in stream only - a uniform buffer is then an argument error - and beyond that the handle is
+ * energy-only (mcb_total_energy). */
 int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, int64_t cap, int64_t *consumed,
                   int64_t *steps_done);
 int mcb_get_stats(mcb_t *h, int chain0, int nchains, mcb_chain_stats *out);

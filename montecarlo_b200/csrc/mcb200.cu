@@ -28,12 +28,14 @@ struct mcb_handle {
     SiteRel rel{};
     int n_chains = 0, device = 0, n_sites = 0;
     bool coul = false, can_step = false, dirty = true, energy_only = false;
+    bool smem_fits = false;  // a chain's image fits in shared memory (every stepping kernel but the global-image k_run_vl2 needs that)
     double *big_e = nullptr, *big_sol = nullptr, *big_out = nullptr; long long *big_n = nullptr, *big_nout = nullptr;
     long long big_blocks = 0; int big_tiles = 0;
     CellGrid cells{};       // cell list of the matrix-free energy (mcb_cells.cuh); nc == 0: not in use
     int ncell = 0;
     VerletBufs vl{};        // neighbour lists of k_run_vl (large boxes); idx == nullptr: not in use
     int vl2_w = 0;          // warps per chain of k_run_vl2: 0 not chosen yet, -1 does not fit
+    bool vl2_global = false; // k_run_vl2 reads the chain's image from global memory instead of staging it
     bool no_vl2 = false;    // MCB200_NO_VL2 (read once, at mcb_create)
     bool trial_pending = false;   // mcb_trial_delta has parked a trial that mcb_commit has not resolved yet
     cudaStream_t stream = nullptr;
@@ -140,7 +142,13 @@ static void setup_geo(mcb_handle *h)
     h->smem_spec_bytes = ((size_t)g.stage_doubles + (size_t)h->lookahead * (g.work_doubles + SPECX_DOUBLES) + 64 + 6 * 64 + 32 + g.Np + 6 * g.Np + 6 * 64 + (g.N + 63) / 64 + 2) * 8;
     // a box whose matrix lives in global memory steps with the neighbour-list kernels, which need less shared memory
     // than k_run_spec's plan (no sin/cos cache); k_run_spec is then only the list-free fall-back and may not fit
-    h->can_step = (g.mat_in_image ? h->smem_spec_bytes : (size_t)vl_smem_doubles(g) * 8) <= 227 * 1024;
+    h->smem_fits = (g.mat_in_image ? h->smem_spec_bytes : (size_t)vl_smem_doubles(g) * 8) <= 227 * 1024;
+    // a larger box still steps with the built-in stream: k_run_vl2 with the image left in global memory (neighbour lists:
+    // 32 < N < 65536), as long as the start-up kernel's per-warp row buffers fit
+    const bool prep_fits = ((size_t)PREP_W * prepare_warp_doubles(g) + 3 * PREP_W) * 8 <= 227 * 1024;
+    const bool lists_possible = !g.mat_in_image && g.N > 32 && g.N < 65536 && h->spec_w == 1 && h->spec_gl == 32 &&
+                                !getenv("MCB200_NO_VERLET") && !getenv("MCB200_NO_VL2");
+    h->can_step = h->smem_fits || (lists_possible && prep_fits);
 }
 
 extern "C" const char *mcb_last_error(const mcb_t *h) { return h ? h->err.c_str() : g_create_err.c_str(); }
@@ -252,6 +260,7 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
     int vl_min_n = 33;
     if (const char *mn = getenv("MCB200_VERLET_MIN_N")) vl_min_n = atoi(mn);   // tuning only
     h->no_vl2 = getenv("MCB200_NO_VL2") != nullptr;
+    if (!h->smem_fits) vl_min_n = 33;   // (the lists are the only way such a box steps)
     if (!h->energy_only && !g.mat_in_image && g.N >= vl_min_n && g.N > 32 && g.N < 65536 && h->spec_w == 1 && h->spec_gl == 32 && !getenv("MCB200_NO_VERLET")) {
         // large box, one step per warp: neighbour lists for k_run_vl (mcb_verlet.cuh)
         h->vl.skin = 2.0;
@@ -287,7 +296,7 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
         const size_t pb = ((size_t)PREP_W * prepare_warp_doubles(g) + 3 * PREP_W) * 8;
         if (set_smem_attr(h, k_prepare<true>, pb) || set_smem_attr(h, k_prepare<false>, pb)) return fail(-1);
     }
-    if (h->can_step) {
+    if (h->can_step && h->smem_fits) {
         int rc = 0;
         rc |= set_smem_attr(h, k_run_steps<false, false>, h->smem_bytes); rc |= set_smem_attr(h, k_run_steps<false, true>, h->smem_bytes);
         rc |= set_smem_attr(h, k_run_steps<true, false>, h->smem_bytes);  rc |= set_smem_attr(h, k_run_steps<true, true>, h->smem_bytes);
@@ -776,39 +785,61 @@ static void launch_run_spec_any(mcb_t *h, long long nsteps, long long *d_steps)
     }
 }
 
-template <int W>
+template <int W, bool IMG_SMEM>
 static void launch_vl2(mcb_t *h, long long nsteps, long long *d_steps)
 {
-    const size_t bytes = (size_t)vl2_smem_doubles(h->g, W) * 8;
-    if (h->coul) k_run_vl2<true, W><<<h->n_chains, 32 * W, bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->work, h->ctl, nsteps, d_steps, h->vl);
-    else k_run_vl2<false, W><<<h->n_chains, 32 * W, bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->work, h->ctl, nsteps, d_steps, h->vl);
+    const size_t bytes = (size_t)vl2_smem_doubles(h->g, W, IMG_SMEM) * 8;
+    if (h->coul) k_run_vl2<true, W, IMG_SMEM><<<h->n_chains, 32 * W, bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->work, h->ctl, nsteps, d_steps, h->vl);
+    else k_run_vl2<false, W, IMG_SMEM><<<h->n_chains, 32 * W, bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->work, h->ctl, nsteps, d_steps, h->vl);
 }
 
-template <int W>
+template <int W, bool IMG_SMEM>
 static int vl2_blocks_per_sm(mcb_t *h)
 {
-    const size_t bytes = (size_t)vl2_smem_doubles(h->g, W) * 8;
+    const size_t bytes = (size_t)vl2_smem_doubles(h->g, W, IMG_SMEM) * 8;
     if (bytes > 227 * 1024) return 0;
-    if (set_smem_attr(h, k_run_vl2<true, W>, bytes) || set_smem_attr(h, k_run_vl2<false, W>, bytes)) return 0;
+    if (set_smem_attr(h, k_run_vl2<true, W, IMG_SMEM>, bytes) || set_smem_attr(h, k_run_vl2<false, W, IMG_SMEM>, bytes)) return 0;
     int nb = 0;
-    cudaError_t e = h->coul ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_run_vl2<true, W>, 32 * W, bytes)
-                            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_run_vl2<false, W>, 32 * W, bytes);
+    cudaError_t e = h->coul ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_run_vl2<true, W, IMG_SMEM>, 32 * W, bytes)
+                            : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_run_vl2<false, W, IMG_SMEM>, 32 * W, bytes);
     return e == cudaSuccess ? nb : 0;
 }
 
-// Warps per chain for k_run_vl2: the widest variant that still keeps every chain resident at once; if none does, the
-// one that puts most warps on an SM.  -1: the kernel does not fit (k_run_vl is used).  MCB200_VL2_W overrides (tuning).
-static int pick_vl2_width(mcb_t *h)
+// Which k_run_vl2 runs a handle: the chain's image staged in shared memory (W = 2-4 warps per chain) or left in global
+// memory (W = 1-4), and how many warps per chain.  Staged: the widest variant that still keeps every chain resident at
+// once; if none does, the one that puts most warps on an SM.  vl2_w = -1: nothing fits (k_run_vl is used).
+// MCB200_VL2_W and MCB200_VL2_IMG=smem|global override (tuning).
+static void pick_vl2_variant(mcb_t *h)
 {
     int dev = 0, nsm = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
-    const int occ[5] = {0, 0, vl2_blocks_per_sm<2>(h), vl2_blocks_per_sm<3>(h), vl2_blocks_per_sm<4>(h)};
-    if (const char *t = getenv("MCB200_VL2_W")) { const int w = atoi(t); if (w >= 2 && w <= 4 && occ[w] > 0) return w; }
-    for (int w = 4; w >= 2; --w) if (occ[w] > 0 && (long long)occ[w] * nsm >= h->n_chains) return w;
+    const int occ_s[5] = {0, 0, vl2_blocks_per_sm<2, true>(h), vl2_blocks_per_sm<3, true>(h), vl2_blocks_per_sm<4, true>(h)};
+    const int occ_g[5] = {0, vl2_blocks_per_sm<1, false>(h), vl2_blocks_per_sm<2, false>(h), vl2_blocks_per_sm<3, false>(h), vl2_blocks_per_sm<4, false>(h)};
+    const char *ti = getenv("MCB200_VL2_IMG"), *tw = getenv("MCB200_VL2_W");
+    const int w_env = tw ? atoi(tw) : 0;
+    if (ti && !strcmp(ti, "global")) {
+        h->vl2_global = true;
+        h->vl2_w = w_env >= 1 && w_env <= 4 && occ_g[w_env] > 0 ? w_env : 1;
+        return;
+    }
+    h->vl2_global = false;
+    if (w_env >= 2 && w_env <= 4 && occ_s[w_env] > 0) { h->vl2_w = w_env; return; }
     int best = -1, best_warps = 0;
-    for (int w = 2; w <= 4; ++w) if (occ[w] * w > best_warps) { best_warps = occ[w] * w; best = w; }
-    return best;
+    for (int w = 4; w >= 2 && best < 0; --w) if (occ_s[w] > 0 && (long long)occ_s[w] * nsm >= h->n_chains) best = w;
+    if (best < 0) for (int w = 2; w <= 4; ++w) if (occ_s[w] * w > best_warps) { best_warps = occ_s[w] * w; best = w; }
+    // Global image instead: with cps chains per SM it keeps min(cps, 16 / W) * W warps on an SM.  Measured on B200
+    // (profiles/vl2_image_r02.txt): a warp reading its image through L1/L2 does about 0.6 of the work of one with the
+    // image staged, so the global variant is taken when it at least doubles the resident warps (N = 810: 1 staged chain
+    // per SM), never at N = 240 (4 staged chains per SM), and always when the image does not fit in shared memory.
+    const int cps = (int)((h->n_chains + nsm - 1) / nsm);
+    int w_g = std::min(4, std::max(1, 16 / std::max(cps, 1)));
+    while (w_g > 1 && occ_g[w_g] == 0) --w_g;
+    const int warps_g = std::min(cps, occ_g[w_g]) * w_g;
+    const int warps_s = best > 0 ? std::min(cps, occ_s[best]) * best : 0;
+    if (ti && !strcmp(ti, "smem") && best > 0) { h->vl2_w = best; return; }
+    if (occ_g[w_g] > 0 && (best < 0 || !h->smem_fits || warps_g >= 2 * warps_s)) { h->vl2_global = true; h->vl2_w = w_g; return; }
+    h->vl2_w = best;
 }
 
 extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, int64_t cap, int64_t *consumed, int64_t *steps_done)
@@ -817,6 +848,7 @@ extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, i
     if (nsteps < 0) return arg_err(h, "mcb_run_steps: nsteps < 0");
     if (!h->can_step) return arg_err(h, "mcb_run_steps: a chain of this size does not fit in shared memory (energy-only mode)");
     if (uniforms && cap < 8) return arg_err(h, "mcb_run_steps: uniform buffer needs cap >= 8 per chain");
+    if (uniforms && !h->smem_fits) return arg_err(h, "mcb_run_steps: a chain of this size does not fit in shared memory and steps with the built-in stream only (uniforms = NULL)");
     CK(h, cudaSetDevice(h->device));
     if (int rc = ensure_prepared(h)) return rc;
     const size_t nc = (size_t)h->n_chains;
@@ -835,16 +867,23 @@ extern "C" int mcb_run_steps(mcb_t *h, int64_t nsteps, const double *uniforms, i
     if (uniforms) { if (h->coul) launch_run_ubuf<true>(h, nsteps, cap, d_consumed, d_steps); else launch_run_ubuf<false>(h, nsteps, cap, d_consumed, d_steps); }
     else {
         CK(h, cudaMemsetAsync(d_consumed, 0, sizeof(long long) * nc, h->stream));
-        if (h->vl.idx && !h->vl2_w && !h->no_vl2) h->vl2_w = pick_vl2_width(h);
+        if (h->vl.idx && !h->vl2_w && !h->no_vl2) pick_vl2_variant(h);
         if (h->vl.idx && h->vl2_w > 0) {
             // W warps per chain, W consecutive steps in flight (mcb_verlet2.cuh)
-            switch (h->vl2_w) {
-                case 4: launch_vl2<4>(h, nsteps, d_steps); break;
-                case 3: launch_vl2<3>(h, nsteps, d_steps); break;
-                default: launch_vl2<2>(h, nsteps, d_steps); break;
+            if (h->vl2_global) switch (h->vl2_w) {
+                case 4: launch_vl2<4, false>(h, nsteps, d_steps); break;
+                case 3: launch_vl2<3, false>(h, nsteps, d_steps); break;
+                case 2: launch_vl2<2, false>(h, nsteps, d_steps); break;
+                default: launch_vl2<1, false>(h, nsteps, d_steps); break;
+            }
+            else switch (h->vl2_w) {
+                case 4: launch_vl2<4, true>(h, nsteps, d_steps); break;
+                case 3: launch_vl2<3, true>(h, nsteps, d_steps); break;
+                default: launch_vl2<2, true>(h, nsteps, d_steps); break;
             }
             h->vl.trust = 1;
         } else if (h->vl.idx) {
+            if (!h->smem_fits) return arg_err(h, "mcb_run_steps: no stepping kernel fits a chain of this size");
             const size_t vb = (size_t)vl_smem_doubles(h->g) * 8;   // (its own size: k_run_spec's plan has grown caches this kernel does not use)
             set_smem_attr(h, k_run_vl<true>, vb); set_smem_attr(h, k_run_vl<false>, vb);
             if (h->coul) k_run_vl<true><<<h->n_chains, 32, vb, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, nsteps, d_steps, h->vl);

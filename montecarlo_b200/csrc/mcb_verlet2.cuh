@@ -28,17 +28,23 @@ constexpr int VL2_MAX_W = 8;
 
 __host__ __device__ inline int vl2_small_slots(const Geo &g) { return VL_K + g.nsolp; }
 __host__ __device__ inline int vl2_list_doubles(int slots) { return (((slots + 1) / 2) + 1) & ~1; }   // ints, padded to 16 bytes
-__host__ __device__ inline int vl2_smem_doubles(const Geo &g, int w)
+__host__ __device__ inline int vl2_smem_doubles(const Geo &g, int w, bool img_smem = true)
 {
     const int small = vl2_small_slots(g);
-    return g.stage_doubles + w * (vl2_list_doubles(small) + 4 * small) + 64 + 6 * 64 + 32 + 2 * VL2_MAX_W + 4 * VL2_MAX_W;
+    return (img_smem ? g.stage_doubles : 0) + w * (vl2_list_doubles(small) + 4 * small) + 64 + 6 * 64 + 32 + 2 * VL2_MAX_W + 4 * VL2_MAX_W;
 }
 
-template <bool COUL, int W>
-__global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteRel rel, double *images, double *matg, double *workg,
+// IMG_SMEM = false: the chain's image (centres of mass, angles, site cache, parameter rows) stays in global memory and
+// is read through L1/L2; shared memory then only holds the work areas and the ring (~6 KB per chain with one warp), so an
+// SM holds up to 16 chains where the staged image allows 4 (N = 240) or 1 (N = 810).  That is the variant for MANY chains
+// per GPU (more chains than all SMs can keep resident with staged images) and allows W = 1: one warp per chain, latency
+// hidden by the other chains' warps instead of by steps in flight.  All warps of a chain sit in one block, so a commit
+// through global memory is visible to the chain's other warps after the batch's closing barrier.
+template <bool COUL, int W, bool IMG_SMEM = true>
+__global__ void __launch_bounds__(32 * W, IMG_SMEM ? (W <= 2 ? 1 : 4) : 16 / W) k_run_vl2(Geo g, SiteRel rel, double *images, double *matg, double *workg,
                                                                     ChainCtl *ctl, long long nsteps, long long *out_steps, VerletBufs vb)
 {
-    static_assert(W >= 2 && W <= VL2_MAX_W, "2..8 warps per chain");
+    static_assert(W >= 1 && W <= VL2_MAX_W && (IMG_SMEM ? W >= 2 : W <= 4), "1..8 warps per chain");
     constexpr int NT = 32 * W;
     extern __shared__ __align__(16) double smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -46,10 +52,11 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
     const int N = g.N, Np = g.Np, MS = g.MS, nsolp = g.nsolp;
     const unsigned lt = (1u << lane) - 1u;
     double *gimg = images + (size_t)c * g.image_doubles;
-    double *img = smem;
-    {
+    double *const img = IMG_SMEM ? smem : gimg;
+    const int stage = IMG_SMEM ? g.stage_doubles : 0;
+    if (IMG_SMEM) {
         const double2 *src = reinterpret_cast<const double2 *>(gimg);
-        double2 *dst = reinterpret_cast<double2 *>(img);
+        double2 *dst = reinterpret_cast<double2 *>(smem);
         for (int k = tid; k < g.stage_doubles / 2; k += NT) dst[k] = src[k];
     }
     double *const mat = matg + (size_t)c * N * MS;
@@ -60,12 +67,12 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
     // shared-memory plan behind the image: one small work area per warp (VL_K + nsolp partner slots: what a list can
     // yield), ring, row sums, exchange.  A step that needs the full scan runs on warp 0 in the chain's global work area.
     const int small = vl2_small_slots(g);
-    double *p = smem + g.stage_doubles + warp * (vl2_list_doubles(small) + 4 * small);
+    double *p = smem + stage + warp * (vl2_list_doubles(small) + 4 * small);
     int *const list = reinterpret_cast<int *>(p);
     double *const epart = p + vl2_list_doubles(small);
     int *const list_g = reinterpret_cast<int *>(workg + (size_t)c * g.work_doubles + g.o_list);
     double *const epart_g = workg + (size_t)c * g.work_doubles + g.o_epart;
-    p = smem + g.stage_doubles + W * (vl2_list_doubles(small) + 4 * small);
+    p = smem + stage + W * (vl2_list_doubles(small) + 4 * small);
     double *const ring_thr = p; p += 64;
     double *const ring_rv = p; p += 6 * 64;
     int *const ring_i = reinterpret_cast<int *>(p); p += 32;
@@ -102,7 +109,7 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
         if (lane == 0) colsum[0] = acc;
         __syncthreads();
         double tot = 0.0;
-        for (int w = 0; w < W; ++w) tot += (smem + g.stage_doubles + w * (vl2_list_doubles(small) + 4 * small) + vl2_list_doubles(small))[0];
+        for (int w = 0; w < W; ++w) tot += (smem + stage + w * (vl2_list_doubles(small) + 4 * small) + vl2_list_doubles(small))[0];
         s.toteng = tot;
         __syncthreads();
     }
@@ -428,7 +435,7 @@ __global__ void __launch_bounds__(32 * W, W <= 2 ? 1 : 4) k_run_vl2(Geo g, SiteR
         __syncthreads();
     }
     if (warp == 0) sum_stats();
-    {
+    if (IMG_SMEM) {
         const int n_mut = g.o_sites + SITE_DOUBLES * N;
         for (int qq = tid; qq < n_mut; qq += NT) gimg[qq] = img[qq];
     }

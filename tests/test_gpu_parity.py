@@ -994,3 +994,69 @@ def test_random_boxes_against_oracle(shipped, case):
         o.run_steps_rng(steps, ol.rng_seed(int(seeds[c])), trace=False)
         _compare_chain(st, c, o.stats(), c_, h_, o)
         assert abs(fresh[c] - st["toteng"][c]) <= RTOL * abs(fresh[c]) + 1e-300
+
+
+@pytest.mark.parametrize("width", ["1", "2", "3", "4"])
+def test_global_image_list_kernel(shipped, width, monkeypatch):
+    """k_run_vl2 with the chain's image left in global memory (MCB200_VL2_IMG=global: the variant for more chains than the
+    SMs can hold with staged images, and for boxes too large to stage) with 1-4 warps per chain: the scenario of
+    test_steps_in_flight_edges - short launches, nadj = 3, a production start inside a batch, a skin that forces full
+    scans - plus the Coulomb sum, get/set of the state between launches and a fresh recompute at the end."""
+    box, system = shipped
+    b = boxio.replicate(box, 2)
+    s = _sys_for(system, b)
+    monkeypatch.setenv("MCB200_VL2_IMG", "global")
+    monkeypatch.setenv("MCB200_VL2_W", width)
+    for skin, conv in (("2.0", 0.0), ("0.2", 0.0), ("1.0", ol.lib().mco_const_conv_intended())):
+        monkeypatch.setenv("MCB200_SKIN", skin)
+        sc = boxio.System(**{**s.__dict__, "conv": conv})
+        eng = _engine(sc, b.n, n_chains=3)
+        eng.set_state(b.com, b.hoek)
+        eng.set_mc_params(nadj=3, start_prod=50)
+        eng.seed(np.array([81, 82, 83], dtype=np.uint64))
+        total = 0
+        for n in (1, 2, 3, 5, 7, 1, 64, 65, 300, 0, 11):
+            eng.run_steps(n)
+            total += n
+            if n == 65:   # the coordinates leave the device and come back: lists are rebuilt, the energies recomputed
+                c0, h0 = eng.get_state()
+                eng.set_state(c0, h0)
+        st = eng.stats()
+        com, hoek = eng.get_state()
+        fresh = eng.total_energy()[0]
+        assert np.all(np.abs(fresh - st["toteng"]) <= RTOL * np.abs(fresh))
+        for c in range(3):
+            o = ol.OracleChain(sc, b.com, b.hoek)
+            o.set_mc_params(nadj=3, start_prod=50)
+            o.total_energy()
+            o.run_steps_rng(total, ol.rng_seed(81 + c), trace=False)
+            so = o.stats()
+            # (set_state in the middle re-anchors TOTENG on a fresh recompute: compare it at the tolerance, the rest exactly)
+            _compare_chain(st, c, so, com, hoek, o)
+
+
+def test_box_too_large_for_shared_memory_steps_from_global_memory(shipped):
+    """N = 1920 (4x4x4 replica): a chain's image (292 KB) cannot be staged in shared memory, so round 1 could only
+    compute its energy.  It now steps with the built-in stream on the global-image kernel; driver-supplied uniforms
+    are refused with a message.  600 steps of two chains against the oracle."""
+    from montecarlo_b200.engine import McbError
+    box, system = shipped
+    b = boxio.replicate(box, 4)
+    s = _sys_for(system, b)
+    eng = _engine(s, b.n, n_chains=2)
+    eng.set_state(b.com, b.hoek)
+    eng.seed(np.array([21, 22], dtype=np.uint64))
+    tot0 = eng.total_energy()[0]
+    eng.run_steps(250); eng.run_steps(350)
+    st = eng.stats()
+    com, hoek = eng.get_state()
+    fresh = eng.total_energy()[0]
+    assert np.all(np.abs(fresh - st["toteng"]) <= RTOL * np.abs(fresh))
+    for c in range(2):
+        o = ol.OracleChain(s, b.com, b.hoek)
+        e0 = o.total_energy()
+        assert abs(tot0[c] - e0) <= RTOL * abs(e0)
+        o.run_steps_rng(600, ol.rng_seed(21 + c), trace=False)
+        _compare_chain(st, c, o.stats(), com, hoek, o)
+    with pytest.raises(McbError):
+        eng.run_steps(5, np.zeros((2, 40)))
