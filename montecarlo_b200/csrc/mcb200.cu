@@ -145,7 +145,7 @@ static void setup_geo(mcb_handle *h)
     h->smem_fits = (g.mat_in_image ? h->smem_spec_bytes : (size_t)vl_smem_doubles(g) * 8) <= 227 * 1024;
     // a larger box still steps with the built-in stream: k_run_vl2 with the image left in global memory (neighbour lists:
     // 32 < N < 65536), as long as the start-up kernel's per-warp row buffers fit
-    const bool prep_fits = ((size_t)PREP_W * prepare_warp_doubles(g) + 3 * PREP_W) * 8 <= 227 * 1024;
+    const bool prep_fits = (size_t)prepare_smem_doubles(g, false) * 8 <= 227 * 1024;
     const bool lists_possible = !g.mat_in_image && g.N > 32 && g.N < 65536 && h->spec_w == 1 && h->spec_gl == 32 &&
                                 !getenv("MCB200_NO_VERLET") && !getenv("MCB200_NO_VL2");
     h->can_step = h->smem_fits || (lists_possible && prep_fits);
@@ -293,8 +293,9 @@ extern "C" int mcb_create(mcb_t **out, const mcb_params *p)
     }
     CKC(cudaMemcpy(h->ctl, ctl.data(), nc * sizeof(ChainCtl), cudaMemcpyHostToDevice));
     if (!h->energy_only) {
-        const size_t pb = ((size_t)PREP_W * prepare_warp_doubles(g) + 3 * PREP_W) * 8;
-        if (set_smem_attr(h, k_prepare<true>, pb) || set_smem_attr(h, k_prepare<false>, pb)) return fail(-1);
+        const size_t pb = (size_t)prepare_smem_doubles(g, prepare_can_stage(g)) * 8;
+        if (prepare_can_stage(g) ? (set_smem_attr(h, k_prepare<true, true>, pb) || set_smem_attr(h, k_prepare<false, true>, pb))
+                                 : (set_smem_attr(h, k_prepare<true, false>, pb) || set_smem_attr(h, k_prepare<false, false>, pb))) return fail(-1);
     }
     if (h->can_step && h->smem_fits) {
         int rc = 0;
@@ -422,9 +423,12 @@ extern "C" int mcb_get_chain_state(mcb_t *h, int chain0, int nchains, double *co
 // ------------------------------------------------------------------------------------------------ energies
 static int launch_prepare(mcb_t *h, int chain0, int nchains, double *d_tot, double *d_esol, long long *d_pairs)
 {
-    const size_t bytes = ((size_t)PREP_W * prepare_warp_doubles(h->g) + 3 * PREP_W) * 8;
-    if (h->coul) k_prepare<true><<<nchains, 32 * PREP_W, bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, chain0, d_tot, d_esol, d_pairs);
-    else k_prepare<false><<<nchains, 32 * PREP_W, bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, chain0, d_tot, d_esol, d_pairs);
+    const int staged = prepare_can_stage(h->g) ? 1 : 0;
+    const size_t bytes = (size_t)prepare_smem_doubles(h->g, staged != 0) * 8;
+#define PREP_LAUNCH(C, S) k_prepare<C, S><<<nchains, 32 * PREP_W, bytes, h->stream>>>(h->g, h->rel, h->images, h->matg, h->ctl, chain0, d_tot, d_esol, d_pairs)
+    if (h->coul) { if (staged) PREP_LAUNCH(true, true); else PREP_LAUNCH(true, false); }
+    else { if (staged) PREP_LAUNCH(false, true); else PREP_LAUNCH(false, false); }
+#undef PREP_LAUNCH
     h->launches++;
     CK(h, cudaGetLastError());
     return 0;

@@ -25,12 +25,21 @@ constexpr double INV_SQRT3 = 0x1.279a74590331dp-1;              // 1.D0/sqrt(3.D
 constexpr int PREP_W = 8;   // warps per chain in k_prepare: rows of the matrix are dealt out to them
 
 __host__ __device__ inline int prepare_warp_doubles(const Geo &g) { return g.Np + ((g.Np + g.nsolp + 1) / 2 + 1 & ~1); }
+// shared memory of a k_prepare block: the warps' row buffers, their partial sums and - when it all fits (N <~ 1000) - a
+// copy of the centres of mass, the site cache and the parameter rows, which every row's gate and site pairs read (from global memory the
+// kernel spent 10 of its 17 cycles per instruction waiting for those loads: profiles/README.md, round 2)
+__host__ __device__ inline int prepare_stage_doubles(const Geo &g) { return 3 * g.Np + SITE_DOUBLES * (g.N + g.nsolp) + (1 + g.nsolp) * 4 * (TAB_ROW + 4); }
+__host__ __device__ inline int prepare_smem_doubles(const Geo &g, bool staged)
+{
+    return PREP_W * prepare_warp_doubles(g) + 3 * PREP_W + 1 + (staged ? prepare_stage_doubles(g) : 0);
+}
+__host__ inline bool prepare_can_stage(const Geo &g) { return (size_t)prepare_smem_doubles(g, true) * 8 <= 100 * 1024; }
 
-template <bool COUL>
+template <bool COUL, bool STAGED>
 __global__ void __launch_bounds__(32 * PREP_W) k_prepare(Geo g, SiteRel rel, double *images, double *matg, ChainCtl *ctl, int chain0,
                                                          double *out_tot, double *out_esol, long long *out_pairs)
 {
-    extern __shared__ __align__(16) double smem[];   // per warp: newrow[Np] + list[Np + nsolp]; then PREP_W x 3 partial sums
+    extern __shared__ __align__(16) double smem[];   // per warp: newrow[Np] + list[Np + nsolp]; then PREP_W x 3 partial sums; then the staged copy
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int c = chain0 + blockIdx.x;
     double *img = images + (size_t)c * g.image_doubles;
@@ -55,11 +64,23 @@ __global__ void __launch_bounds__(32 * PREP_W) k_prepare(Geo g, SiteRel rel, dou
         }
     }
     __syncthreads();
+    if (STAGED) {   // the rows below read centres of mass and sites from shared memory
+        double *const scom = smem + ((PREP_W * prepare_warp_doubles(g) + 3 * PREP_W + 1) & ~1), *const ssites = scom + 3 * Np;
+        for (int q = tid; q < 3 * Np; q += 32 * PREP_W) scom[q] = p.com[q];
+        const double2 *src = reinterpret_cast<const double2 *>(p.sites);
+        double2 *dst = reinterpret_cast<double2 *>(ssites);
+        for (int q = tid; q < SITE_DOUBLES / 2 * (N + g.nsolp); q += 32 * PREP_W) dst[q] = src[q];
+        double *const stab = ssites + SITE_DOUBLES * (N + g.nsolp), *const stq = stab + (1 + g.nsolp) * 4 * TAB_ROW;
+        for (int q = tid; q < (1 + g.nsolp) * 4 * TAB_ROW; q += 32 * PREP_W) stab[q] = p.tabAB[q];
+        for (int q = tid; q < (1 + g.nsolp) * 16; q += 32 * PREP_W) stq[q] = p.tabQ[q];
+        p.com = scom; p.sites = ssites; p.tabAB = stab; p.tabQ = stq;
+        __syncthreads();
+    }
 
     // row i = molecule i as MOL1 against every j < i: each unordered pair once, the larger index as MOL1
     const int a = lane & 3;
     long long pairs = 0;
-    double esum = 0.0;
+    double esum = 0.0, racc = 0.0;
     for (int i = warp; i < N; i += PREP_W) {
         double sx = p.sites[SITE_DOUBLES * i + 3 * a], sy = p.sites[SITE_DOUBLES * i + 3 * a + 1],
                sz = p.sites[SITE_DOUBLES * i + 3 * a + 2];
@@ -70,18 +91,15 @@ __global__ void __launch_bounds__(32 * PREP_W) k_prepare(Geo g, SiteRel rel, dou
         if (lane == 0) { p.energy[i] = e_sol; mat[(size_t)i * g.MS + i] = 0.0; }
         for (int j = lane; j < i; j += 32) {
             double v = p.newrow[j];
+            racc += v;
             mat[(size_t)i * g.MS + j] = v;
             mat[(size_t)j * g.MS + i] = v;
         }
         __syncwarp();
     }
-    __syncthreads();
-    // calcEnergy (MonteCarlo.F90:988-1004): thread-parallel partial sums combined in a fixed order => deterministic
-    double acc = 0.0;
-    for (int i = warp; i < N; i += PREP_W)
-        for (int j = i + 1 + lane; j < N; j += 32) acc += mat[(size_t)i * g.MS + j];
-    for (int i = tid; i < N; i += 32 * PREP_W) acc += p.energy[i];
-    acc = warp_sum(acc);
+    // calcEnergy (MonteCarlo.F90:988-1004): every pair energy once plus every ENERGY(i), summed as the rows are formed
+    // (per lane, then per warp, then over the warps in a fixed order => deterministic; no second pass over the matrix)
+    const double acc = warp_sum(racc) + esum;
     if (lane == 0) { red[3 * warp] = acc; red[3 * warp + 1] = esum; red[3 * warp + 2] = (double)pairs; }
     __syncthreads();
     if (tid == 0) {
