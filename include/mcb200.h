@@ -145,6 +145,11 @@ int mcb_seed_chains(mcb_t *h, int chain0, int nchains, const uint64_t *seeds);
  * (may be NULL) receives how many it used, steps_done[c] (may be NULL) how many steps it made.  With
  * uniforms, consumed and steps_done all NULL the call only enqueues the kernel on the handle's stream and
  * returns; any later call that reads results (mcb_get_stats, mcb_get_chain_state, ...) waits for it.
+ * DELTA: with a uniform buffer METROPOLIS tests DELTA = (TOTENG + dE) - TOTENG, the reference's subtraction of two
+ * totals (MonteCarlo.F90:415-428, :726); with the built-in stream it tests dE as summed.  The two differ by the
+ * rounding of TOTENG + dE (at most an ulp of TOTENG), which can change a decision only where the exponent is within
+ * that distance of its threshold - the margin BASELINE's parity rule leaves open.  Both clamp +Inf and NaN and let
+ * -Inf pass, as the reference does.
  * Box sizes: up to ~1400 molecules a chain's coordinates and site cache are staged in the SM's shared memory and both
  * kinds of stream work; a larger box (up to 65535 molecules, as long as the pair matrices fit in the GPU's memory) steps
  * with the built-in stream only - a uniform buffer is then an argument error - and beyond that the handle is
