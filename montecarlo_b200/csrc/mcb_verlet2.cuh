@@ -47,7 +47,9 @@ __global__ void __launch_bounds__(32 * W, IMG_SMEM ? (W <= 2 ? 1 : 4) : 16 / W) 
     static_assert(W >= 1 && W <= VL2_MAX_W && (IMG_SMEM ? W >= 2 : W <= 4), "1..8 warps per chain");
     constexpr int NT = 32 * W;
     extern __shared__ __align__(16) double smem[];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    int tid = threadIdx.x;
+    asm volatile("" : "+r"(tid));   // (kept in a register: the compiler otherwise reads the special register again at every use)
+    const int lane = tid & 31, warp = tid >> 5;
     const int c = blockIdx.x;
     const int N = g.N, Np = g.Np, MS = g.MS, nsolp = g.nsolp;
     const unsigned lt = (1u << lane) - 1u;
@@ -59,7 +61,10 @@ __global__ void __launch_bounds__(32 * W, IMG_SMEM ? (W <= 2 ? 1 : 4) : 16 / W) 
         double2 *dst = reinterpret_cast<double2 *>(smem);
         for (int k = tid; k < g.stage_doubles / 2; k += NT) dst[k] = src[k];
     }
-    double *const mat = matg + (size_t)c * N * MS;
+    double *mat_ = matg + (size_t)c * N * MS;
+    asm volatile("" : "+l"(mat_));    // (same: one 64-bit register pair instead of the multiply chain at every use)
+    __builtin_assume(__isGlobal(mat_));
+    double *const mat = mat_;
     double *const com = img + g.o_com, *const hoek = img + g.o_hoek, *const energy = img + g.o_energy;
     double *const sites = img + g.o_sites;
     const double *const tabAB = img + g.o_tabAB, *const tabQ = img + g.o_tabQ;
@@ -225,13 +230,17 @@ __global__ void __launch_bounds__(32 * W, IMG_SMEM ? (W <= 2 ? 1 : 4) : 16 / W) 
             p_rfx = vref[i]; p_rfy = vref[Np + i]; p_rfz = vref[2 * Np + i];
         }
         const int cnt = lists_on ? p_cnt : -1;
+        // the list's second half (candidates 32..63) is rarely in use - a list holds ~24 - and the same on every lane:
+        // everything that concerns it sits behind this flag instead of being computed on empty slots
+        const bool two = cnt > 32;
         int cj[2];
         double cold[2];
-#pragma unroll
-        for (int q = 0; q < 2; ++q) cj[q] = lane + 32 * q < cnt ? p_idx[q] : -1;
+        cj[0] = lane < cnt ? p_idx[0] : -1;
+        cj[1] = two && lane + 32 < cnt ? p_idx[1] : -1;
         const double rfx = p_rfx, rfy = p_rfy, rfz = p_rfz;
-#pragma unroll
-        for (int q = 0; q < 2; ++q) cold[q] = cj[q] >= 0 ? mat[(size_t)i * MS + cj[q]] : 0.0;
+        cold[0] = cj[0] >= 0 ? mat[(size_t)i * MS + cj[0]] : 0.0;
+        cold[1] = 0.0;
+        if (two) cold[1] = cj[1] >= 0 ? mat[(size_t)i * MS + cj[1]] : 0.0;
         if (lists_on) {   // this warp's step of the next batch if all steps of this one are committed
             const int in = ring_i[(ring0 + k + W) & 63];
             p_cnt = vcnt[in];
@@ -264,16 +273,20 @@ __global__ void __launch_bounds__(32 * W, IMG_SMEM ? (W <= 2 ? 1 : 4) : 16 / W) 
             if (use_list) {
 #pragma unroll
                 for (int q = 0; q < 2; ++q) {   // every lane computes a distance (empty lanes on molecule 0), the guard selects
-                    const int jj = cj[q] >= 0 ? cj[q] : 0;
-                    const double r2 = pair_r2(com[jj] - ncx, com[Np + jj] - ncy, com[2 * Np + jj] - ncz, g);
-                    cin[q] = !((cj[q] >= 0 ? r2 : DBL_HUGE) > g.cut2);
+                    if (q == 0 || two) {
+                        const int jj = cj[q] >= 0 ? cj[q] : 0;
+                        const double r2 = pair_r2(com[jj] - ncx, com[Np + jj] - ncy, com[2 * Np + jj] - ncz, g);
+                        cin[q] = !((cj[q] >= 0 ? r2 : DBL_HUGE) > g.cut2);
+                    }
                 }
 #pragma unroll
                 for (int q = 0; q < 2; ++q) {
-                    const unsigned b = __ballot_sync(FULL, cin[q]);
-                    cslot[q] = nsolp + nn + __popc(b & lt);
-                    if (cin[q]) list[cslot[q]] = cj[q];
-                    nn += __popc(b);
+                    if (q == 0 || two) {
+                        const unsigned b = __ballot_sync(FULL, cin[q]);
+                        cslot[q] = nsolp + nn + __popc(b & lt);
+                        if (cin[q]) list[cslot[q]] = cj[q];
+                        nn += __popc(b);
+                    }
                 }
             } else {
                 for (int c0 = 0; c0 < N; c0 += 32) {
@@ -303,21 +316,11 @@ __global__ void __launch_bounds__(32 * W, IMG_SMEM ? (W <= 2 ? 1 : 4) : 16 / W) 
             // entries all belong to listed candidates (a partner inside the cutoff is inside cutoff + skin), so with a
             // list the old row is summed from the entries fetched above; the full scan reads the whole row.
             double old_part = lane == 0 ? e_old : 0.0;
-            if (use_list) old_part += cold[0] + cold[1];
+            if (use_list) old_part += two ? cold[0] + cold[1] : cold[0];
             else for (int j = lane; j < N; j += 32) old_part += mat[(size_t)i * MS + j];
             dE = lane_tot - old_part;
             __syncwarp();
             const double *const ep = use_list ? epart : epart_g;
-            // what an accepted move would write for this lane's candidates: formed here, in the shadow of the reduction
-            if (use_list) {
-#pragma unroll
-                for (int q = 0; q < 2; ++q) {
-                    const int sl = cin[q] ? cslot[q] : 0;
-                    const double2 e01 = *reinterpret_cast<const double2 *>(epart + 4 * sl), e23 = *reinterpret_cast<const double2 *>(epart + 4 * sl + 2);
-                    cval[q] = cin[q] ? (e01.x + e01.y) + (e23.x + e23.y) : 0.0;
-                    cchg[q] = cj[q] >= 0 && (cin[q] || cold[q] != 0.0);
-                }
-            }
             if (sub < nsolp) esol = ep[4 * sub + a];
             if (nsolp > 8) {
 #pragma unroll 1
@@ -379,9 +382,20 @@ __global__ void __launch_bounds__(32 * W, IMG_SMEM ? (W <= 2 ? 1 : 4) : 16 / W) 
         //      nothing shared is read-modified-written (the old row is summed from the matrix entries, see above)
         if (warp < progress && accept) {
             if (use_list) {
+                // what the move writes for this lane's candidates is only formed here, for the steps that are committed
+                // (about half of them): the SMs that hold four chains are bound by the instructions they issue
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                    if (q == 0 || two) {
+                        const int sl = cin[q] ? cslot[q] : 0;
+                        const double2 e01 = *reinterpret_cast<const double2 *>(epart + 4 * sl), e23 = *reinterpret_cast<const double2 *>(epart + 4 * sl + 2);
+                        cval[q] = cin[q] ? (e01.x + e01.y) + (e23.x + e23.y) : 0.0;
+                        cchg[q] = cj[q] >= 0 && (cin[q] || cold[q] != 0.0);
+                    }
+                }
 #pragma unroll
                 for (int q = 0; q < 2; ++q)
-                    if (cchg[q]) {   // SS(i,j) = SS(j,i) = EN inside the cutoff (:819-820), 0 for a partner that left it
+                    if ((q == 0 || two) && cchg[q]) {   // SS(i,j) = SS(j,i) = EN inside the cutoff (:819-820), 0 for a partner that left it
                         const int j = cj[q];
                         mat[(size_t)i * MS + j] = cval[q]; mat[(size_t)j * MS + i] = cval[q];
                     }
@@ -407,14 +421,12 @@ __global__ void __launch_bounds__(32 * W, IMG_SMEM ? (W <= 2 ? 1 : 4) : 16 / W) 
         }
         // ---- bookkeeping in step order: every warp tracks what steers the chain (accepted moves of the adaptation
         //      window, list validity); the energy statistics only live on warp 0, whose lane 0 writes them back
+        nacc += __popc(acc_valid);                                  // acc_valid: the accepted steps among the first `progress`
+        {
+            unsigned far_m = 0u;                                     // their molecule now sits more than skin/2 from its build position
 #pragma unroll
-        for (int gg = 0; gg < W; ++gg) {
-            if (gg < progress) {
-                const Vl2X x = xs[gg];
-                const bool acc = (x.flags & 1) != 0;
-                nacc += acc;
-                if (lists_on && acc && (x.flags & 8)) need_rebuild = true;   // the molecule now sits more than skin/2 from its build position
-            }
+            for (int gg = 0; gg < W; ++gg) far_m |= (xs[gg].flags & 8) ? 1u << gg : 0u;
+            if (lists_on && (acc_valid & far_m)) need_rebuild = true;
         }
         // the energy statistics of this batch (warp 0) are summed at the top of the next one, off the stretch where
         // every other warp waits at the batch's last barrier

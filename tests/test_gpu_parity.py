@@ -961,6 +961,7 @@ SWEEP = [
     (48, 9.0, 0, False, 400),      # global matrix, neighbour lists, no solute
     (64, 10.0, 7, True, 400),
     (100, 12.0, 11, False, 400),
+    (100, 9.5, 11, False, 400),    # ~45 listed candidates per molecule: the second half of the 64-entry lists is in use
     (150, 9.0, 11, False, 300),    # dense: neighbour lists overflow their 64 entries -> the full scan takes over
 ]
 
