@@ -2,20 +2,25 @@
 //
 // A box whose matrix lives in global memory needs ~45-55 KB of shared memory per chain, so an SM holds four chains
 // and, with one warp per chain, one warp per scheduler: every global-memory and shuffle latency of a step is
-// exposed.  Here warp w evaluates step k+w of the same chain against the same committed state.  Each warp w > 0
-// also decides, for every earlier step j of the batch, whether its own step would have seen anything that step
-// j's move changes: the same molecule; molecule i_j inside the cutoff of its trial position before or after i_j's
-// own move; molecule i_j inside the cutoff of its molecule's committed position before or after (that entry of
-// the old row feeds dE).  It can do so alone, because step j's trial position only needs the pre-drawn ring and the
-// committed coordinates.  After one exchange through shared memory every warp knows every decision: step k+w
-// stands if all steps before it stand and no ACCEPTED one of them fired the test above; standing accepted steps
-// are committed one after the other, each by its own warp.  The first step that does not stand, and everything
-// after it, is evaluated again in the next batch with the same uniforms, so the chain is the sequential one,
-// decision for decision.  In a box of 240 molecules about one step in eleven fails against its predecessor.
+// exposed.  Here warp w evaluates step k+w of the same chain against the same committed state and posts dE, its
+// flags and its trial position.  After ONE exchange barrier every warp answers, for all ordered pairs (ga < gb) of
+// the batch at once (four lanes per pair, one distance test each), whether step ga's move would change anything
+// step gb looked at: the same molecule; molecule i_ga inside the cutoff of gb's trial position before or after
+// i_ga's own move; molecule i_ga inside the cutoff of gb's molecule as committed, before or after (that entry of
+// the old row feeds dE).  Step k+w stands if all steps before it stand and no ACCEPTED one of them fired the test;
+// the standing accepted steps touch disjoint molecules and matrix entries and are committed all at once, each by
+// its own warp.  The first step that does not stand, and everything after it, is evaluated again in the next
+// batch with the same uniforms, so the chain is the sequential one, decision for decision.  In a box of 240
+// molecules a batch of four commits 3.78 steps on average.
 //
 // Every warp works in a small area (VL_K + nsolp partner slots: what a neighbour list can yield); a step that
 // cannot use its list (trial position beyond skin/2, overflowed list, lists off) is evaluated by warp 0 only, with
 // the full scan, in the chain's global work area - the batch is then that one step.
+//
+// With 512 chains on 148 SMs the SMs that hold four chains are ~88 % issue-bound (profiles/vl2_image_r02.txt), so
+// the loop is written for few instructions rather than for short latency: work on the rarely used second half of a
+// candidate list sits behind a warp-uniform flag, what a commit writes is only formed for committed steps, and the
+// thread id and the matrix pointer are pinned in registers (the compiler re-derives them at every use otherwise).
 #pragma once
 
 #include "mcb_verlet.cuh"
