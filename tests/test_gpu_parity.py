@@ -757,12 +757,13 @@ def test_coulomb_stepping_kernels(shipped, path, monkeypatch):
     assert np.all(np.abs(fresh - st["toteng"]) <= RTOL * np.abs(fresh))
 
 
-@pytest.mark.parametrize("coulomb", [False, True])
-def test_single_step_mode_on_global_matrix_box(shipped, coulomb):
+@pytest.mark.parametrize("coulomb,kbox,nmoves", [(False, 2, 1200), (True, 2, 1200), (False, 4, 150)])
+def test_single_step_mode_on_global_matrix_box(shipped, coulomb, kbox, nmoves):
     """mcb_trial_delta / mcb_commit on the N = 240 replica (k_trial / k_commit with the matrix in global memory; with
-    conv != 0 also k_trial<true>): 1200 trial moves drawn the way MCINIT draws them, the oracle deciding."""
+    conv != 0 also k_trial<true>) and on the N = 1920 replica, whose image does not fit in shared memory: trial moves
+    drawn the way MCINIT draws them, the oracle deciding."""
     box, system = shipped
-    b = boxio.replicate(box, 2)
+    b = boxio.replicate(box, kbox)
     s = _coulomb_system(system, b) if coulomb else _sys_for(system, b)
     eng = _engine(s, b.n, n_chains=2)
     eng.set_state(b.com, b.hoek)
@@ -771,7 +772,7 @@ def test_single_step_mode_on_global_matrix_box(shipped, coulomb):
     assert abs(o.total_energy() - e0[0]) <= RTOL * abs(e0[0])
     rng = np.random.default_rng(123)
     nacc = 0
-    for k in range(1200):
+    for k in range(nmoves):
         u = rng.random(8)
         used, tr = o.step(u)                      # MCINIT + calculateLJ + METROPOLIS in the oracle
         i = int(tr[4]); accepted = tr[5] != 0.0
@@ -792,7 +793,7 @@ def test_single_step_mode_on_global_matrix_box(shipped, coulomb):
         assert abs(d_e[0] - (tr[0] - tr[1])) <= RTOL * scale, (k, d_e[0], tr[0] - tr[1])
         eng.commit([1 if accepted else 0, 0])
         nacc += accepted
-    assert nacc > 100
+    assert nacc > nmoves // 12
     st = eng.stats()
     so = o.stats()
     assert abs(st["toteng"][0] - so["toteng"]) <= RTOL * abs(so["toteng"]) and st["toteng"][1] == e0[1]
